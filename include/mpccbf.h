@@ -1,0 +1,190 @@
+/* mpccbf.h — C ABI of the B200-native batched MPC-CBF QP path.
+ *
+ * Drop-in boundary for the reference's per-agent, per-control-step QP build+solve
+ * (paths relative to /root/reference/workspace/lib):
+ *   S-ctl  bool mpc_cbf::ConnectivityIMPCCBF<double,3>::optimize(result_curves, current_states,
+ *          self_idx, ref_positions)        mpc_cbf/include/mpc_cbf/controller/ConnectivityIMPCCBF.h:58-60
+ *   S-qp   qpcpp::SolveStatus qpcpp::Solver<double>::solve(qpcpp::Problem<double>&)
+ *                                           qpcpp/include/qpcpp/solvers/Solver.h:27-37
+ * The reference has no FFI layer; these entry points are what a C++ shim with the two signatures
+ * above binds (see INTEGRATION.md and mpc-cbf_b200/host/). Plain pointers and sizes only; no
+ * exceptions cross the ABI; solver outcomes are data (status[]), not errors.
+ *
+ * All arithmetic is FP64 (the reference instantiates <double,3U> only:
+ * mpc_cbf/src/controller/ConnectivityIMPCCBF.cpp:222).
+ *
+ * Error convention: 0 = OK; negative = invalid argument / CUDA error, message available from
+ * mpccbf_last_error() (thread-local). There is NO CPU fallback: every compute entry point
+ * returns MPCCBF_ERR_CUDA when no sm_100-class device is usable.
+ */
+#ifndef MPCCBF_H
+#define MPCCBF_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPCCBF_OK 0
+#define MPCCBF_ERR_INVALID (-1)   /* bad argument / failed config validation            */
+#define MPCCBF_ERR_CUDA (-2)      /* CUDA runtime error or no usable device             */
+#define MPCCBF_ERR_UNSUPPORTED (-3) /* configuration outside what the kernels implement */
+#define MPCCBF_ERR_ALLOC (-4)
+
+/* qpcpp::SolveStatus codes (qpcpp/include/qpcpp/solvers/Solver.h:13-21), same order. */
+#define MPCCBF_STATUS_OPTIMAL 0
+#define MPCCBF_STATUS_FEASIBLE 1
+#define MPCCBF_STATUS_UNBOUNDED 2
+#define MPCCBF_STATUS_INFEASIBLE 3
+#define MPCCBF_STATUS_ERROR 4
+#define MPCCBF_STATUS_UNKNOWN 5
+#define MPCCBF_STATUS_INFEASIBLEORUNBOUNDED 6
+/* "not attempted": IMPC iteration skipped because an earlier one was not OPTIMAL
+ * (ConnectivityIMPCCBF.cpp:203-211 breaks out of the loop). */
+#define MPCCBF_STATUS_SKIPPED 7
+
+/* Which solver the controller path uses. */
+#define MPCCBF_SOLVER_AUTO 0     /* reduced when the structure allows, else dense ADMM     */
+#define MPCCBF_SOLVER_REDUCED 1  /* fused null-space active-set kernel (C^3 cubic pieces)   */
+#define MPCCBF_SOLVER_DENSE 2    /* full-space assembly + one-CTA-per-QP ADMM/OSQP kernel   */
+
+/* Configuration: union of the reference's parameter structs
+ *   mpc::PiecewiseBezierParams / MPCParams / TuningParams / PhysicalLimits
+ *        mpc/include/mpc/optimization/PiecewiseBezierMPCQPOperations.h:17-41
+ *   ConnectivityIMPCCBF::IMPCParams   mpc_cbf/include/mpc_cbf/controller/ConnectivityIMPCCBF.h:39-45
+ *   cbf::ConnectivityCBFParams {dmin,dmax}; gamma is hard-coded 5.0 at
+ *        cbf/src/detail/ConnectivityCBF.cpp:62
+ * JSON keys: workspace/experiments/config/config.md:5-55. */
+typedef struct mpccbf_config {
+    double h;                 /* mpc_params.h   : MPC step                              */
+    double Ts;                /* mpc_params.Ts  : control (rollout) step                */
+    int32_t k_hor;            /* mpc_params.k_hor                                       */
+    int32_t num_pieces;       /* bezier_params.num_pieces                               */
+    int32_t num_ctrl_pts;     /* bezier_params.num_control_points (4 = cubic)           */
+    int32_t continuity_degree;/* bezier_params.bezier_continuity_upto_degree            */
+    double piece_max_param;   /* bezier_params.piece_max_parameter                      */
+    double w_pos_err;         /* mpc_tuning.w_pos_err                                   */
+    double w_u_eff;           /* mpc_tuning.w_u_eff                                     */
+    int32_t spd_f;            /* mpc_tuning.spd_f                                       */
+    int32_t cbf_horizon;      /* cbf_params.cbf_horizon                                 */
+    double v_min[3], v_max[3], a_min[3], a_max[3]; /* physical_limits                   */
+    double d_min, d_max;      /* cbf_params.d_min / d_max                               */
+    double cbf_gamma;         /* 5.0 in the reference                                   */
+    int32_t impc_iter;        /* cbf_params.impc_iter                                   */
+    int32_t slack_mode;       /* cbf_params.slack_mode                                  */
+    double slack_cost;        /* cbf_params.slack_cost                                  */
+    double slack_decay;       /* cbf_params.slack_decay_rate                            */
+    int32_t num_agents;       /* robots per scenario (tasks.so length)                  */
+    int32_t max_scenarios;    /* batch capacity of the handle                           */
+    int32_t device;           /* CUDA device ordinal                                    */
+    int32_t solver;           /* MPCCBF_SOLVER_*                                        */
+    double feas_tol;          /* row feasibility tolerance (<=0: default 1e-9)          */
+    /* dense ADMM kernel knobs (<=0: defaults) */
+    int32_t admm_max_iter;    /* default 4000                                           */
+    int32_t admm_check_every; /* default 10                                             */
+    double admm_eps;          /* abs = rel termination tolerance, default 1e-7          */
+    double admm_rho;          /* initial rho, default 0.1                               */
+    double admm_sigma;        /* default 1e-6                                           */
+} mpccbf_config;
+
+typedef struct mpccbf_handle mpccbf_handle;
+
+/* Fills *cfg with workspace/experiments/config/base_config.json (the effective parameters
+ * after preprocess.py: K=16, 3 cubic pieces, C^3, d_min 2.0, H=2, 2 IMPC iterations). */
+void mpccbf_config_default(mpccbf_config* cfg);
+
+/* Same validation rules (and messages) as common/include/common/parsing.hpp:50-75,121-132,
+ * 195-213. Returns MPCCBF_OK or MPCCBF_ERR_INVALID (message in mpccbf_last_error()). */
+int mpccbf_config_validate(const mpccbf_config* cfg);
+
+/* Reads a reference experiment JSON (base_config.json schema) into *cfg and, when `so`/`sf` are
+ * non-NULL, the tasks' start/goal poses ([num_agents][3], up to cap_agents). Host only. */
+int mpccbf_config_from_json(const char* path, mpccbf_config* cfg, double* so, double* sf,
+                            int32_t cap_agents);
+
+/* Builds the constant tables (ConnectivityIMPCCBF ctor + PiecewiseBezierMPCQPOperations ctor:
+ * ConnectivityIMPCCBF.cpp:9-44, PiecewiseBezierMPCQPOperations.cpp:9-38), uploads them and
+ * allocates device workspaces for max_scenarios x num_agents. */
+int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out);
+int mpccbf_destroy(mpccbf_handle* h);
+
+const char* mpccbf_last_error(void);
+const char* mpccbf_version(void);
+
+/* Decision-vector length n = num_pieces*3*num_ctrl_pts, layout x[piece*3c + axis*c + cp]
+ * (BezierQPOperations.cpp:37, PiecewiseBezierMPCQPGenerator.cpp:9-34). */
+int32_t mpccbf_num_decision_vars(const mpccbf_handle* h);
+/* Which solver the controller path resolved to (MPCCBF_SOLVER_REDUCED / _DENSE). */
+int32_t mpccbf_active_solver(const mpccbf_handle* h);
+
+/* Batched control step == ConnectivityIMPCCBF::optimize for every agent of every scenario
+ * (Jacobi: all agents see the same state snapshot).
+ *   states   [S][N][6]  (pos3, vel3)            device pointer
+ *   targets  [S][N][3]  goal, replicated over the horizon like
+ *                       MPCCBFFormationControl_example.cpp:144        device pointer
+ *   ctrl_pts [S][N][n]  control points of the LAST successful IMPC iterate (what the caller of
+ *                       optimize uses: trajs.back()); zero-filled if none   device pointer
+ *   status   [S][N][impc_iter]  SolveStatus per IMPC iteration (SKIPPED after a failure)
+ *   n_curves [S][N]     number of curves optimize would have pushed (may be NULL)
+ *   objective[S][N]     x'Px+q'x of the last successful iterate (may be NULL)
+ * Asynchronous on `cuda_stream` (a cudaStream_t, NULL = default stream). */
+int mpccbf_step_batch(mpccbf_handle* h, int32_t num_scenarios, const double* states,
+                      const double* targets, double* ctrl_pts, int32_t* status, int32_t* n_curves,
+                      double* objective, void* cuda_stream);
+
+/* Same, HOST pointers: copies in, runs, copies out, synchronises (this is the call the
+ * reference-facing plugin makes and what bench.py times as `e2e`). */
+int mpccbf_step_batch_host(mpccbf_handle* h, int32_t num_scenarios, const double* states,
+                           const double* targets, double* ctrl_pts, int32_t* status,
+                           int32_t* n_curves, double* objective);
+
+/* Single-agent drop-in for S-ctl (host pointers): states [N][6], ref [3*k_hor] (only used as a
+ * per-step reference: ref[3k..3k+2] is the target at horizon step k), ctrl_pts [impc_iter][n]
+ * receives EVERY successful iterate in order (result_curves), *n_curves how many,
+ * status [impc_iter]. Returns MPCCBF_OK even when the QP is infeasible (see status). */
+int mpccbf_optimize_one(mpccbf_handle* h, const double* states, int32_t self_idx,
+                        const double* ref, double* ctrl_pts, int32_t* n_curves, int32_t* status);
+
+/* S-qp: batch of `batch` dense QPs of identical shape, reference objective convention
+ *      min x'Px + q'x   s.t.  l <= A x <= u ,  lb <= x <= ub        (|bound| >= 1e20: none)
+ * P [batch][n][n], q [batch][n], A [batch][m][n], l,u [batch][m], lb,ub [batch][n] or NULL,
+ * x [batch][n], objective [batch] (may be NULL), status [batch], iters [batch] (may be NULL).
+ * HOST pointers; one CTA per QP on the device (ADMM/OSQP iteration with a shared-memory
+ * Cholesky of P~+sigma I+rho A'A, followed by an active-set polish). */
+int mpccbf_solve_qp_dense(mpccbf_handle* h, int32_t batch, int32_t n, int32_t m, const double* P,
+                          const double* q, const double* A, const double* l, const double* u,
+                          const double* lb, const double* ub, double* x, double* objective,
+                          int32_t* status, int32_t* iters);
+
+/* Sub-kernel K1: pairwise safety HOCBF rows for every ordered (ego, neighbour) pair at the
+ * CURRENT states (iter-0 rows, ConnectivityIMPCCBF.cpp:135-141; closed form of
+ * ConnectivityCBF.cpp:152-198). rows [S][N][N-1][4] = (ax, ay, az=0, b) meaning a.u + b >= 0,
+ * neighbour order = ascending agent index skipping ego. Device pointers, async on stream. */
+int mpccbf_cbf_rows(mpccbf_handle* h, int32_t num_scenarios, const double* states, double* rows,
+                    void* cuda_stream);
+
+/* Sub-kernel K3: advance every agent along its curve by one MPC step, i.e. the state after the
+ * h/Ts rollout sub-steps of MPCCBFFormationControl_example.cpp:191-205 without noise:
+ * next[S][N][6] = (curve(h), curve'(h)); agents whose n_curves == 0 keep their position with zero
+ * velocity (:208-221). Also writes the horizon-shifted warm start (control points of the same
+ * cubic re-parametrised to start at t = h) to warm[S][N][n] when non-NULL. Device pointers. */
+int mpccbf_rollout(mpccbf_handle* h, int32_t num_scenarios, const double* states,
+                   const double* ctrl_pts, const int32_t* n_curves, double* next_states,
+                   double* warm, void* cuda_stream);
+
+/* Constant tables for tests / integrators (host copies, row-major). name is one of
+ * "U_basis" [3K][n], "P" [n][n], "E" [me][n] (equality rows: eval pos/vel at 0, continuity),
+ * "A_fix" [6K][n] (acc rows then vel rows), "h_samples" [K], "Z" [n][r], "Y" [n][6],
+ * "H_red" [r][r]. Returns the number of doubles written, or the required count when
+ * out == NULL, negative on error. */
+int64_t mpccbf_get_table(const mpccbf_handle* h, const char* name, double* out, int64_t cap);
+
+/* Counters since create (may be NULL individually). */
+int mpccbf_get_counters(const mpccbf_handle* h, int64_t* kernel_launches, int64_t* qps_solved);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPCCBF_H */
