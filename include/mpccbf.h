@@ -78,7 +78,8 @@ typedef struct mpccbf_config {
     double slack_decay;       /* cbf_params.slack_decay_rate                            */
     int32_t num_agents;       /* robots per scenario (tasks.so length)                  */
     int32_t max_scenarios;    /* batch capacity of the handle                           */
-    int32_t device;           /* CUDA device ordinal                                    */
+    int32_t device;           /* CUDA device ordinal; -1 = host-only handle (tables and
+                               * validation only, every compute call returns ERR_CUDA)   */
     int32_t solver;           /* MPCCBF_SOLVER_*                                        */
     double feas_tol;          /* row feasibility tolerance (<=0: default 1e-9)          */
     /* dense ADMM kernel knobs (<=0: defaults) */
@@ -168,18 +169,45 @@ int mpccbf_cbf_rows(mpccbf_handle* h, int32_t num_scenarios, const double* state
 /* Sub-kernel K3: advance every agent along its curve by one MPC step, i.e. the state after the
  * h/Ts rollout sub-steps of MPCCBFFormationControl_example.cpp:191-205 without noise:
  * next[S][N][6] = (curve(h), curve'(h)); agents whose n_curves == 0 keep their position with zero
- * velocity (:208-221). Also writes the horizon-shifted warm start (control points of the same
- * cubic re-parametrised to start at t = h) to warm[S][N][n] when non-NULL. Device pointers. */
+ * velocity (:208-221). n_curves may be NULL (all agents have a curve). next may alias states.
+ * Device pointers, async on stream. */
 int mpccbf_rollout(mpccbf_handle* h, int32_t num_scenarios, const double* states,
                    const double* ctrl_pts, const int32_t* n_curves, double* next_states,
-                   double* warm, void* cuda_stream);
+                   void* cuda_stream);
+
+/* Agent-sharded control step (one scenario's agents split across GPUs):
+ * solves only agents [agent_begin, agent_begin + agent_count) of every scenario. states is the
+ * FULL snapshot [S][N][6] (after the all-gather); targets/ctrl_pts/status/n_curves/objective are
+ * indexed [S][agent_count][...]. Device pointers, async on stream. */
+int mpccbf_step_agents(mpccbf_handle* h, int32_t num_scenarios, int32_t agent_begin,
+                       int32_t agent_count, const double* states, const double* targets,
+                       double* ctrl_pts, int32_t* status, int32_t* n_curves, double* objective,
+                       void* cuda_stream);
+
+/* Active-set iteration counts of the last mpccbf_step_batch / _agents call on this handle:
+ * iters [S][agents][impc_iter] (device pointer, valid until the next call), for flop accounting. */
+const int32_t* mpccbf_last_iteration_counts(const mpccbf_handle* h);
+
+/* Measures the FP64 FMA throughput of the device with a register-resident DFMA loop (the
+ * roofline denominator of the solve kernel). Returns TFLOP/s, or a negative error code. */
+double mpccbf_measure_fp64_tflops(mpccbf_handle* h);
 
 /* Constant tables for tests / integrators (host copies, row-major). name is one of
- * "U_basis" [3K][n], "P" [n][n], "E" [me][n] (equality rows: eval pos/vel at 0, continuity),
+ * "U_basis" [3K][n], "V_basis" [3K][n], "P" [n][n], "E" [me][n] (equality rows: eval pos/vel at 0, continuity),
  * "A_fix" [6K][n] (acc rows then vel rows), "h_samples" [K], "Z" [n][r], "Y" [n][6],
  * "H_red" [r][r]. Returns the number of doubles written, or the required count when
  * out == NULL, negative on error. */
 int64_t mpccbf_get_table(const mpccbf_handle* h, const char* name, double* out, int64_t cap);
+
+/* Linear cost q [n] of one agent, q = Phi'Q(2 A0 x0 - 2 ref) (positionErrorPenaltyCost,
+ * mpc/src/optimization/PiecewiseBezierMPCQPOperations.cpp:64-91): x0 [6], ref [3K]. Host only;
+ * with table "P" this is everything an integrator needs to assemble the reference's QP. */
+int mpccbf_linear_cost(const mpccbf_handle* h, const double* x0, const double* ref, double* q);
+
+/* Pinned host memory for the host-pointer entry points (cudaHostAlloc / cudaFreeHost), so a
+ * C++ caller without the CUDA runtime can give mpccbf_step_batch_host DMA-able buffers. */
+void* mpccbf_host_alloc(size_t bytes);
+void mpccbf_host_free(void* p);
 
 /* Counters since create (may be NULL individually). */
 int mpccbf_get_counters(const mpccbf_handle* h, int64_t* kernel_launches, int64_t* qps_solved);

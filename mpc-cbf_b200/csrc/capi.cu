@@ -1,0 +1,589 @@
+// C ABI of libmpccbf.so (include/mpccbf.h). Thin: argument checks, table upload, launches.
+// No CPU fallback anywhere: without a usable sm_100-class device every compute entry point
+// returns MPCCBF_ERR_CUDA.
+#include <cuda_runtime.h>
+
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/mpccbf.h"
+#include "kernels.h"
+#include "tables.hpp"
+
+namespace mpccbf {
+
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+
+}  // namespace mpccbf
+
+using namespace mpccbf;
+
+struct mpccbf_handle {
+    mpccbf_config cfg;
+    HostTables tab;
+    DevTables dev;
+    RolloutConst rc;
+    bool has_device = false;
+    int device = -1;
+    int sm_count = 0;
+    int solver = MPCCBF_SOLVER_REDUCED;
+    int lanes = 32;
+    cudaStream_t stream = nullptr;
+    // device copies of the tables
+    double *d_tmpl = nullptr, *d_yw = nullptr, *d_vr = nullptr, *d_kr = nullptr;
+    std::vector<double> h_tmpl, h_yw, h_vr, h_kr;  // host copies (uploaded at create)
+    // workspaces for the host-pointer entry points (capacity: max_scenarios * num_agents)
+    double *w_states = nullptr, *w_targets = nullptr, *w_ctrl = nullptr, *w_obj = nullptr;
+    int32_t *w_status = nullptr, *w_ncurves = nullptr, *w_iters = nullptr;
+    // single-agent workspace (optimize_one)
+    double *o_states = nullptr, *o_ref = nullptr, *o_ctrl = nullptr, *o_all = nullptr;
+    int32_t* o_status = nullptr;
+    int64_t launches = 0, qps = 0;
+};
+
+#define CUDA_TRY(expr)                                                                     \
+    do {                                                                                   \
+        cudaError_t _e = static_cast<cudaError_t>(expr);                                   \
+        if (_e != cudaSuccess) {                                                           \
+            set_error(std::string(#expr) + ": " + cudaGetErrorString(_e));                 \
+            return MPCCBF_ERR_CUDA;                                                        \
+        }                                                                                  \
+    } while (0)
+
+namespace {
+
+int require_device(const mpccbf_handle* h) {
+    if (!h) {
+        set_error("handle is NULL");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (!h->has_device) {
+        set_error("no CUDA device bound to this handle (host-only handle, device = -1): there is no CPU fallback");
+        return MPCCBF_ERR_CUDA;
+    }
+    return MPCCBF_OK;
+}
+
+template <typename T>
+int upload(const std::vector<T>& v, T** out) {
+    CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(out), sizeof(T) * std::max<size_t>(v.size(), 1)));
+    CUDA_TRY(cudaMemcpy(*out, v.data(), sizeof(T) * v.size(), cudaMemcpyHostToDevice));
+    return MPCCBF_OK;
+}
+
+int build_device_tables(mpccbf_handle* h) {
+    const HostTables& t = h->tab;
+    DevTables& d = h->dev;
+    std::memset(&d, 0, sizeof(d));
+    d.K = t.K;
+    d.p = t.p;
+    d.c = t.c;
+    d.m1 = t.m1;
+    d.n = t.n;
+    d.N = h->cfg.num_agents;
+    d.H = h->cfg.cbf_horizon;
+    d.iters = h->cfg.impc_iter;
+    for (int ax = 0; ax < 3; ++ax) {
+        d.lim_lo[0][ax] = h->cfg.a_min[ax];
+        d.lim_hi[0][ax] = h->cfg.a_max[ax];
+        d.lim_lo[1][ax] = h->cfg.v_min[ax];
+        d.lim_hi[1][ax] = h->cfg.v_max[ax];
+    }
+    d.dmin2 = h->cfg.d_min * h->cfg.d_min;
+    d.gamma = h->cfg.cbf_gamma;
+    d.feas_tol = h->cfg.feas_tol > 0 ? h->cfg.feas_tol : 1e-9;
+    // rollout constants: t = h with the reference's lower_bound piece rule
+    {
+        RolloutConst& rc = h->rc;
+        std::memset(&rc, 0, sizeof(rc));
+        rc.n = t.n;
+        rc.c = t.c;
+        double cum = 0.0;
+        int piece = 0;
+        double prev = 0.0;
+        for (int i = 0; i < t.p; ++i) {
+            prev = cum;
+            cum = (i == 0) ? h->cfg.piece_max_param : cum + h->cfg.piece_max_param;
+            piece = i;
+            if (!(cum < h->cfg.h)) break;  // first cumulative end >= t
+        }
+        const double local = std::min(h->cfg.piece_max_param, (piece == 0) ? h->cfg.h : h->cfg.h - prev);
+        rc.piece = piece;
+        xreal row[8];
+        if (t.c <= 8) {
+            bernstein_deriv(t.c, h->cfg.piece_max_param, local, 0, row);
+            for (int j = 0; j < t.c; ++j) rc.b0[j] = static_cast<double>(row[j]);
+            bernstein_deriv(t.c, h->cfg.piece_max_param, local, 1, row);
+            for (int j = 0; j < t.c; ++j) rc.b1[j] = static_cast<double>(row[j]);
+        }
+    }
+    if (!(t.reducible && t.r1 == 2)) return MPCCBF_OK;
+    const int K = t.K;
+    d.max_gi = 50 * (6 + 12 * K + (d.N - 1) * d.H) + 100;
+    for (int i = 0; i < 2; ++i) {
+        for (int j = 0; j < 2; ++j) {
+            d.Vs[i][j] = static_cast<double>(t.Vs(i, j));
+            d.Kc[i][j] = static_cast<double>(t.Kc(i, j));
+        }
+        xreal sv = 0.0L, sk = 0.0L;
+        for (int k = 0; k < K; ++k) {
+            sv += t.Vr(i, k);
+            sk += t.Kr(i, k);
+        }
+        d.Vt[i] = static_cast<double>(sv);
+        d.Kt[i] = static_cast<double>(sk);
+    }
+    std::vector<double>&tmpl = h->h_tmpl, &yw = h->h_yw, &vr = h->h_vr, &kr = h->h_kr;
+    tmpl.assign(static_cast<size_t>(3) * K * kTmplStride, 0.0);
+    yw.assign(static_cast<size_t>(t.m1) * 4, 0.0);
+    vr.assign(2 * K, 0.0);
+    kr.assign(2 * K, 0.0);
+    for (int dd = 0; dd < 3; ++dd) {
+        xreal nmax = 0.0L;
+        for (int k = 0; k < K; ++k)
+            nmax = std::max(nmax, std::sqrt(t.Ct[dd](k, 0) * t.Ct[dd](k, 0) + t.Ct[dd](k, 1) * t.Ct[dd](k, 1)));
+        for (int k = 0; k < K; ++k) {
+            double* e = &tmpl[(static_cast<size_t>(dd) * K + k) * kTmplStride];
+            const xreal nrm = std::sqrt(t.Ct[dd](k, 0) * t.Ct[dd](k, 0) + t.Ct[dd](k, 1) * t.Ct[dd](k, 1));
+            const bool constant_row = !(nrm > 1e-12L * std::max(nmax, 1e-300L));
+            // rows that do not depend on the free variables (e.g. velocity at t = 0, pinned by the
+            // equality rows) get an exactly zero normal and an infinite score when violated
+            e[0] = constant_row ? 0.0 : static_cast<double>(t.Ct[dd](k, 0));
+            e[1] = constant_row ? 0.0 : static_cast<double>(t.Ct[dd](k, 1));
+            e[2] = static_cast<double>(t.Ot[dd](k, 0));
+            e[3] = static_cast<double>(t.Ot[dd](k, 1));
+            e[4] = constant_row ? static_cast<double>(INFINITY) : static_cast<double>(1.0L / nrm);
+            e[5] = 0.0;
+        }
+    }
+    for (int i = 0; i < t.m1; ++i) {
+        yw[4 * i + 0] = static_cast<double>(t.Y1(i, 0));
+        yw[4 * i + 1] = static_cast<double>(t.Y1(i, 1));
+        yw[4 * i + 2] = static_cast<double>(t.W1(i, 0));
+        yw[4 * i + 3] = static_cast<double>(t.W1(i, 1));
+    }
+    for (int i = 0; i < 2; ++i)
+        for (int k = 0; k < K; ++k) {
+            vr[i * K + k] = static_cast<double>(t.Vr(i, k));
+            kr[i * K + k] = static_cast<double>(t.Kr(i, k));
+        }
+    if (h->has_device) {
+        int rc;
+        if ((rc = upload(tmpl, &h->d_tmpl)) != MPCCBF_OK) return rc;
+        if ((rc = upload(yw, &h->d_yw)) != MPCCBF_OK) return rc;
+        if ((rc = upload(vr, &h->d_vr)) != MPCCBF_OK) return rc;
+        if ((rc = upload(kr, &h->d_kr)) != MPCCBF_OK) return rc;
+        d.tmpl = h->d_tmpl;
+        d.yw = h->d_yw;
+        d.Vr = h->d_vr;
+        d.Kr = h->d_kr;
+    } else {  // host-only handle: tables stay on the host (table queries, tests/emul)
+        d.tmpl = tmpl.data();
+        d.yw = yw.data();
+        d.Vr = vr.data();
+        d.Kr = kr.data();
+    }
+    return MPCCBF_OK;
+}
+
+int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_count, const double* states,
+             const double* targets, int ref_mode, double* ctrl, double* ctrl_all, int32_t* status,
+             int32_t* n_curves, double* objective, int32_t* iters, cudaStream_t stream) {
+    if (h->solver != MPCCBF_SOLVER_REDUCED) {
+        set_error("controller path: this configuration does not reduce to the 6-dof form (needs cubic pieces with "
+                  "C^3 continuity and slack_mode = false); use mpccbf_solve_qp_dense for the assembled QP");
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    StepArgs a;
+    a.states = states;
+    a.targets = targets;
+    a.ctrl_pts = ctrl;
+    a.ctrl_all = ctrl_all;
+    a.status = status;
+    a.n_curves = n_curves;
+    a.objective = objective;
+    a.gi_iters = iters;
+    a.num_qp = S * agent_count;
+    a.agent_begin = agent_begin;
+    a.agent_count = agent_count;
+    a.ref_mode = ref_mode;
+    CUDA_TRY(launch_impc_reduced(h->dev, a, h->lanes, h->sm_count, stream));
+    h->launches += 1;
+    h->qps += static_cast<int64_t>(a.num_qp) * h->cfg.impc_iter;
+    return MPCCBF_OK;
+}
+
+__global__ void dfma_peak_kernel(double* out, int iters, double a, double b) {
+    double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; ++i) {
+        x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+        x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+    }
+    const double s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+    if (s == 123.456) out[0] = s;  // keeps the chain alive without a store in practice
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* mpccbf_last_error(void) { return g_error.c_str(); }
+const char* mpccbf_version(void) { return "mpccbf-b200 0.1 (sm_100a)"; }
+
+int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
+    if (!cfg || !out) {
+        set_error("mpccbf_create: NULL argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    *out = nullptr;
+    int rc = mpccbf_config_validate(cfg);
+    if (rc != MPCCBF_OK) return rc;
+    mpccbf_handle* h = new (std::nothrow) mpccbf_handle();
+    if (!h) {
+        set_error("out of host memory");
+        return MPCCBF_ERR_ALLOC;
+    }
+    h->cfg = *cfg;
+    if (h->cfg.cbf_gamma <= 0) h->cfg.cbf_gamma = 5.0;
+    if (!h->tab.build(h->cfg)) {
+        set_error(h->tab.error);
+        delete h;
+        return MPCCBF_ERR_INVALID;
+    }
+    const bool can_reduce = h->tab.reducible && h->tab.r1 == 2 && !h->cfg.slack_mode && h->cfg.num_agents >= 1;
+    if (cfg->solver == MPCCBF_SOLVER_REDUCED && !can_reduce) {
+        set_error("MPCCBF_SOLVER_REDUCED requested but the configuration does not reduce to the 6-dof form");
+        delete h;
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    h->solver = (cfg->solver == MPCCBF_SOLVER_DENSE || !can_reduce) ? MPCCBF_SOLVER_DENSE : MPCCBF_SOLVER_REDUCED;
+    if (const char* env = std::getenv("MPCCBF_LANES")) {
+        const int w = std::atoi(env);
+        if (w == 32 || w == 8 || w == 1) h->lanes = w;
+    }
+    h->device = cfg->device;
+    if (cfg->device >= 0) {
+        int count = 0;
+        cudaError_t e = cudaGetDeviceCount(&count);
+        if (e != cudaSuccess || cfg->device >= count) {
+            set_error(std::string("no usable CUDA device ") + std::to_string(cfg->device) + ": " +
+                      (e != cudaSuccess ? cudaGetErrorString(e) : "ordinal out of range") +
+                      " (there is no CPU fallback)");
+            delete h;
+            return MPCCBF_ERR_CUDA;
+        }
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, cfg->device) != cudaSuccess || prop.major < 10) {
+            set_error("device is not sm_100-class (kernels are built for sm_100a only)");
+            delete h;
+            return MPCCBF_ERR_CUDA;
+        }
+        if (cudaSetDevice(cfg->device) != cudaSuccess) {
+            set_error("cudaSetDevice failed");
+            delete h;
+            return MPCCBF_ERR_CUDA;
+        }
+        h->sm_count = prop.multiProcessorCount;
+        h->has_device = true;
+        if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) {
+            set_error("cudaStreamCreate failed");
+            delete h;
+            return MPCCBF_ERR_CUDA;
+        }
+    }
+    rc = build_device_tables(h);
+    if (rc != MPCCBF_OK) {
+        mpccbf_destroy(h);
+        return rc;
+    }
+    if (h->has_device) {
+        const size_t B = static_cast<size_t>(cfg->max_scenarios) * cfg->num_agents;
+        const size_t n = h->tab.n, it = cfg->impc_iter, K = cfg->k_hor, N = cfg->num_agents;
+        bool ok = true;
+        ok &= cudaMalloc(&h->w_states, sizeof(double) * B * 6) == cudaSuccess;
+        ok &= cudaMalloc(&h->w_targets, sizeof(double) * B * 3) == cudaSuccess;
+        ok &= cudaMalloc(&h->w_ctrl, sizeof(double) * B * n) == cudaSuccess;
+        ok &= cudaMalloc(&h->w_obj, sizeof(double) * B) == cudaSuccess;
+        ok &= cudaMalloc(&h->w_status, sizeof(int32_t) * B * it) == cudaSuccess;
+        ok &= cudaMalloc(&h->w_ncurves, sizeof(int32_t) * B) == cudaSuccess;
+        ok &= cudaMalloc(&h->w_iters, sizeof(int32_t) * B * it) == cudaSuccess;
+        ok &= cudaMalloc(&h->o_states, sizeof(double) * N * 6) == cudaSuccess;
+        ok &= cudaMalloc(&h->o_ref, sizeof(double) * 3 * K) == cudaSuccess;
+        ok &= cudaMalloc(&h->o_ctrl, sizeof(double) * n) == cudaSuccess;
+        ok &= cudaMalloc(&h->o_all, sizeof(double) * n * it) == cudaSuccess;
+        ok &= cudaMalloc(&h->o_status, sizeof(int32_t) * (it + 1 + it)) == cudaSuccess;
+        if (!ok) {
+            set_error("device workspace allocation failed");
+            mpccbf_destroy(h);
+            return MPCCBF_ERR_ALLOC;
+        }
+    }
+    *out = h;
+    return MPCCBF_OK;
+}
+
+int mpccbf_destroy(mpccbf_handle* h) {
+    if (!h) return MPCCBF_OK;
+    if (h->has_device) {
+        cudaSetDevice(h->device);
+        void* ptrs[] = {h->d_tmpl, h->d_yw, h->d_vr, h->d_kr, h->w_states, h->w_targets, h->w_ctrl, h->w_obj,
+                        h->w_status, h->w_ncurves, h->w_iters, h->o_states, h->o_ref, h->o_ctrl, h->o_all, h->o_status};
+        for (void* p : ptrs)
+            if (p) cudaFree(p);
+        if (h->stream) cudaStreamDestroy(h->stream);
+    }
+    delete h;
+    return MPCCBF_OK;
+}
+
+int32_t mpccbf_num_decision_vars(const mpccbf_handle* h) { return h ? h->tab.n : 0; }
+int32_t mpccbf_active_solver(const mpccbf_handle* h) { return h ? h->solver : 0; }
+
+void* mpccbf_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+        set_error("cudaHostAlloc failed");
+        return nullptr;
+    }
+    return p;
+}
+void mpccbf_host_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+int mpccbf_step_agents(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_count,
+                       const double* states, const double* targets, double* ctrl_pts, int32_t* status,
+                       int32_t* n_curves, double* objective, void* cuda_stream) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (S < 0 || agent_begin < 0 || agent_count < 0 || agent_begin + agent_count > h->cfg.num_agents ||
+        !states || !targets || !ctrl_pts || !status) {
+        set_error("mpccbf_step_agents: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (static_cast<int64_t>(S) * agent_count > static_cast<int64_t>(h->cfg.max_scenarios) * h->cfg.num_agents) {
+        set_error("num_scenarios exceeds the handle's max_scenarios");
+        return MPCCBF_ERR_INVALID;
+    }
+    CUDA_TRY(cudaSetDevice(h->device));
+    return run_step(h, S, agent_begin, agent_count, states, targets, 0, ctrl_pts, nullptr, status, n_curves,
+                    objective, h->w_iters, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mpccbf_step_batch(mpccbf_handle* h, int32_t S, const double* states, const double* targets,
+                      double* ctrl_pts, int32_t* status, int32_t* n_curves, double* objective,
+                      void* cuda_stream) {
+    if (!h) {
+        set_error("handle is NULL");
+        return MPCCBF_ERR_INVALID;
+    }
+    return mpccbf_step_agents(h, S, 0, h->cfg.num_agents, states, targets, ctrl_pts, status, n_curves, objective,
+                              cuda_stream);
+}
+
+const int32_t* mpccbf_last_iteration_counts(const mpccbf_handle* h) { return h ? h->w_iters : nullptr; }
+
+int mpccbf_step_batch_host(mpccbf_handle* h, int32_t S, const double* states, const double* targets,
+                           double* ctrl_pts, int32_t* status, int32_t* n_curves, double* objective) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (S < 0 || S > h->cfg.max_scenarios || !states || !targets || !ctrl_pts || !status) {
+        set_error("mpccbf_step_batch_host: invalid argument (num_scenarios must be <= max_scenarios)");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (S == 0) return MPCCBF_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    const size_t B = static_cast<size_t>(S) * h->cfg.num_agents, n = h->tab.n, it = h->cfg.impc_iter;
+    cudaStream_t st = h->stream;
+    CUDA_TRY(cudaMemcpyAsync(h->w_states, states, sizeof(double) * B * 6, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(h->w_targets, targets, sizeof(double) * B * 3, cudaMemcpyHostToDevice, st));
+    rc = run_step(h, S, 0, h->cfg.num_agents, h->w_states, h->w_targets, 0, h->w_ctrl, nullptr, h->w_status,
+                  h->w_ncurves, h->w_obj, h->w_iters, st);
+    if (rc != MPCCBF_OK) return rc;
+    CUDA_TRY(cudaMemcpyAsync(ctrl_pts, h->w_ctrl, sizeof(double) * B * n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(status, h->w_status, sizeof(int32_t) * B * it, cudaMemcpyDeviceToHost, st));
+    if (n_curves) CUDA_TRY(cudaMemcpyAsync(n_curves, h->w_ncurves, sizeof(int32_t) * B, cudaMemcpyDeviceToHost, st));
+    if (objective) CUDA_TRY(cudaMemcpyAsync(objective, h->w_obj, sizeof(double) * B, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return MPCCBF_OK;
+}
+
+int mpccbf_optimize_one(mpccbf_handle* h, const double* states, int32_t self_idx, const double* ref,
+                        double* ctrl_pts, int32_t* n_curves, int32_t* status) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    const int N = h->cfg.num_agents, K = h->cfg.k_hor, n = h->tab.n, it = h->cfg.impc_iter;
+    if (!states || !ref || !ctrl_pts || !n_curves || !status || self_idx < 0 || self_idx >= N) {
+        set_error("mpccbf_optimize_one: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    CUDA_TRY(cudaMemcpyAsync(h->o_states, states, sizeof(double) * N * 6, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(h->o_ref, ref, sizeof(double) * 3 * K, cudaMemcpyHostToDevice, st));
+    int32_t* d_status = h->o_status;
+    int32_t* d_nc = h->o_status + it;
+    int32_t* d_iters = h->o_status + it + 1;
+    rc = run_step(h, 1, self_idx, 1, h->o_states, h->o_ref, 1, h->o_ctrl, h->o_all, d_status, d_nc, nullptr, d_iters, st);
+    if (rc != MPCCBF_OK) return rc;
+    std::vector<int32_t> hs(it + 1);
+    CUDA_TRY(cudaMemcpyAsync(hs.data(), d_status, sizeof(int32_t) * (it + 1), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    for (int i = 0; i < it; ++i) status[i] = hs[i];
+    *n_curves = hs[it];
+    if (hs[it] > 0) CUDA_TRY(cudaMemcpy(ctrl_pts, h->o_all, sizeof(double) * n * hs[it], cudaMemcpyDeviceToHost));
+    return MPCCBF_OK;
+}
+
+int mpccbf_solve_qp_dense(mpccbf_handle* h, int32_t batch, int32_t n, int32_t m, const double* P,
+                          const double* q, const double* A, const double* l, const double* u,
+                          const double* lb, const double* ub, double* x, double* objective,
+                          int32_t* status, int32_t* iters) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (batch < 0 || n < 1 || m < 0 || !P || !q || (m > 0 && (!A || !l || !u)) || !x || !status) {
+        set_error("mpccbf_solve_qp_dense: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    CUDA_TRY(cudaSetDevice(h->device));
+    return dense_qp_solve_host(h, batch, n, m, P, q, A, l, u, lb, ub, x, objective, status, iters);
+}
+
+int mpccbf_cbf_rows(mpccbf_handle* h, int32_t S, const double* states, double* rows, void* cuda_stream) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (S < 0 || !states || !rows) {
+        set_error("mpccbf_cbf_rows: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(launch_cbf_rows(states, rows, S, h->cfg.num_agents, h->cfg.d_min * h->cfg.d_min, h->cfg.cbf_gamma,
+                             h->sm_count, static_cast<cudaStream_t>(cuda_stream)));
+    h->launches += 1;
+    return MPCCBF_OK;
+}
+
+int mpccbf_rollout(mpccbf_handle* h, int32_t S, const double* states, const double* ctrl_pts,
+                   const int32_t* n_curves, double* next_states, void* cuda_stream) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (S < 0 || !states || !ctrl_pts || !next_states) {
+        set_error("mpccbf_rollout: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (h->tab.c > 8) {
+        set_error("mpccbf_rollout: more than 8 control points per piece is not supported");
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(launch_rollout(states, ctrl_pts, n_curves, next_states, S * h->cfg.num_agents, h->rc,
+                            static_cast<cudaStream_t>(cuda_stream)));
+    h->launches += 1;
+    return MPCCBF_OK;
+}
+
+int64_t mpccbf_get_table(const mpccbf_handle* h, const char* name, double* out, int64_t cap) {
+    if (!h || !name) {
+        set_error("mpccbf_get_table: NULL argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    const std::string nm(name);
+    std::vector<double> v;
+    const HostTables& t = h->tab;
+    if (nm == "U_basis") v = t.full_U();
+    else if (nm == "V_basis") v = t.full_basis(1);
+    else if (nm == "P") v = t.full_P();
+    else if (nm == "E") v = t.full_E();
+    else if (nm == "A_fix") v = t.full_Afix();
+    else if (nm == "h_samples") v = t.h_samples;
+    else if (nm == "Z" && t.reducible) v = t.full_Z();
+    else if (nm == "Y" && t.reducible) v = t.full_Y();
+    else if (nm == "H_red" && t.reducible) v = t.full_Hred();
+    else {
+        set_error("mpccbf_get_table: unknown table '" + nm + "'");
+        return MPCCBF_ERR_INVALID;
+    }
+    const int64_t cnt = static_cast<int64_t>(v.size());
+    if (!out) return cnt;
+    if (cap < cnt) {
+        set_error("mpccbf_get_table: buffer too small");
+        return MPCCBF_ERR_INVALID;
+    }
+    std::memcpy(out, v.data(), sizeof(double) * v.size());
+    return cnt;
+}
+
+int mpccbf_linear_cost(const mpccbf_handle* h, const double* x0, const double* ref, double* q) {
+    if (!h || !x0 || !ref || !q) {
+        set_error("mpccbf_linear_cost: NULL argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    h->tab.linear_cost(x0, ref, q);
+    return MPCCBF_OK;
+}
+
+int mpccbf_get_counters(const mpccbf_handle* h, int64_t* kernel_launches, int64_t* qps_solved) {
+    if (!h) return MPCCBF_ERR_INVALID;
+    if (kernel_launches) *kernel_launches = h->launches;
+    if (qps_solved) *qps_solved = h->qps;
+    return MPCCBF_OK;
+}
+
+#ifdef MPCCBF_HOST_EMUL
+// Test-only entry points (tests/emul/libmpccbf_emul.so): the per-agent device function run on the
+// host for CPU-only CI. NOT part of include/mpccbf.h and NOT compiled into libmpccbf.so.
+int mpccbf_emul_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_count, int32_t ref_mode,
+                     const double* states, const double* targets, double* ctrl_pts, double* ctrl_all,
+                     int32_t* status, int32_t* n_curves, double* objective, int32_t* iters) {
+    if (!h || h->has_device || h->solver != MPCCBF_SOLVER_REDUCED) {
+        set_error("mpccbf_emul_step: needs a host-only (device = -1) reducible handle");
+        return MPCCBF_ERR_INVALID;
+    }
+    StepArgs a;
+    a.states = states;
+    a.targets = targets;
+    a.ctrl_pts = ctrl_pts;
+    a.ctrl_all = ctrl_all;
+    a.status = status;
+    a.n_curves = n_curves;
+    a.objective = objective;
+    a.gi_iters = iters;
+    a.num_qp = S * agent_count;
+    a.agent_begin = agent_begin;
+    a.agent_count = agent_count;
+    a.ref_mode = ref_mode;
+    emul_impc_reduced_host(h->dev, a);
+    return MPCCBF_OK;
+}
+#endif
+
+double mpccbf_measure_fp64_tflops(mpccbf_handle* h) {
+    if (require_device(h) != MPCCBF_OK) return MPCCBF_ERR_CUDA;
+    if (cudaSetDevice(h->device) != cudaSuccess) return MPCCBF_ERR_CUDA;
+    double* d = nullptr;
+    if (cudaMalloc(&d, 8) != cudaSuccess) return MPCCBF_ERR_CUDA;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int blocks = h->sm_count * 8, threads = 256, iters = 20000;
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {
+        cudaEventRecord(e0, h->stream);
+        dfma_peak_kernel<<<blocks, threads, 0, h->stream>>>(d, iters, 1.0000001, 1e-9);
+        cudaEventRecord(e1, h->stream);
+        if (cudaEventSynchronize(e1) != cudaSuccess) break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double flops = 2.0 * 8.0 * iters * static_cast<double>(blocks) * threads;
+        if (rep > 0 && ms > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    return best;
+}
+
+}  // extern "C"
