@@ -1,0 +1,73 @@
+"""CPU-only: the fused kernel's per-agent device function, compiled for the host
+(tests/emul/libmpccbf_emul.so, -DMPCCBF_HOST_EMUL), against the oracle. This checks the
+active-set logic of the CUDA source in a container without a GPU; the real kernel is checked by
+tests/test_gpu_parity.py (-m gpu)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, swarm
+from parity import check_step, dense_scenarios
+
+
+@pytest.fixture(scope="module")
+def emul(M):
+    d = os.path.join(ROOT, "tests", "emul")
+    subprocess.run(["make", "-C", d], check=True, stdout=subprocess.DEVNULL)
+    L = M.lib(os.path.join(d, "libmpccbf_emul.so"))
+    L.mpccbf_emul_step.argtypes = [C.c_void_p] + [C.c_int32] * 4 + [C.c_void_p] * 8
+    return L
+
+
+def run_emul(M, L, cfg, states, targets):
+    cfg = cfg.copy(device=-1)
+    h = M.Handle(cfg, library=L)
+    assert h.solver == M.SOLVER_REDUCED
+    S, N = states.shape[:2]
+    it = cfg.impc_iter
+    out = dict(ctrl_pts=np.zeros((S, N, h.n)), status=np.zeros((S, N, it), np.int32),
+               n_curves=np.zeros((S, N), np.int32), objective=np.zeros((S, N)))
+    iters = np.zeros((S, N, it), np.int32)
+    st, tg = np.ascontiguousarray(states), np.ascontiguousarray(targets)
+    rc = L.mpccbf_emul_step(h._h, S, 0, N, 0, st.ctypes.data, tg.ctypes.data, out["ctrl_pts"].ctypes.data, None,
+                            out["status"].ctypes.data, out["n_curves"].ctypes.data, out["objective"].ctypes.data,
+                            iters.ctypes.data)
+    assert rc == 0
+    out["iters"] = iters
+    h.close()
+    return out
+
+
+def test_two_agent_swap(M, O, emul):
+    cfg = M.default_config()
+    st = np.array([[[2, 2, 0, 0, 0, 0], [-2, -2, 0, 0, 0, 0]]], float)
+    tg = np.array([[[-2, -2, 0], [2, 2, 0]]], float)
+    got = run_emul(M, emul, cfg, st, tg)
+    oc = O.base_config()
+    r = check_step(O, oc, O.get_table(oc, "U_basis"), st, tg, got)
+    assert r["n_infeasible"] == 0
+    assert abs(got["objective"][0, 0] + 1378.9905) < 1e-3
+
+
+@pytest.mark.parametrize("K,p,N,S", [(16, 3, 4, 24), (20, 4, 16, 6), (10, 2, 8, 8)])
+def test_free_space_swarm(M, O, emul, K, p, N, S):
+    cfg = M.default_config(k_hor=K, num_pieces=p, d_min=0.8, num_agents=N)
+    st, tg = swarm(S, N, seed=K * 100 + N)
+    got = run_emul(M, emul, cfg, st, tg)
+    oc = O.base_config(k_hor=K, num_pieces=p, d_min=0.8, num_agents=N)
+    check_step(O, oc, O.get_table(oc, "U_basis"), st, tg, got, check_viol_max=8)
+
+
+@pytest.mark.parametrize("N,seed", [(4, 1), (9, 2), (16, 3)])
+def test_dense_active_cbf_and_infeasible(M, O, emul, N, seed):
+    cfg = M.default_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N)
+    st, tg = dense_scenarios(12, N, seed, 0.8, spread=1.2, vmax=1.5)
+    st[0, 0, 3] = 2.5  # |v0| > v_max: the velocity row at k = 0 contradicts the initial-velocity equality
+    got = run_emul(M, emul, cfg, st, tg)
+    oc = O.base_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N)
+    r = check_step(O, oc, O.get_table(oc, "U_basis"), st, tg, got, check_viol_max=16)
+    assert got["status"][0, 0, 0] == M.STATUS_INFEASIBLE and got["status"][0, 0, 1] == M.STATUS_SKIPPED
+    assert got["iters"].max() > 4  # CBF rows were active somewhere

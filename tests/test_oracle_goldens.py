@@ -1,0 +1,104 @@
+"""Pins the CPU oracle against every known answer the reference's own tests hold for the path
+ and against the REAL reference code compiled into oracle/_ref. CPU only."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+
+
+@pytest.fixture(scope="module")
+def gold():
+    with open(os.path.join(GOLDEN, "reference_goldens.json")) as f:
+        return json.load(f)
+
+
+def test_safety_cbf_goldens(O, gold):
+    # cbf/tests/TestInitSafetyCBF.cpp:50-143 (EXPECT_NEAR 1e-6; the closed form does far better)
+    g = gold["safety_cbf"]
+    for case in g["cases"]:
+        for prec in (0, 1):
+            a, b = O.safety_cbf_row(case["ego"], case["nbr"], g["dmin"], g["gamma"], prec=prec)
+            assert np.allclose(a, case["Ac"], atol=1e-12, rtol=0), case["name"]
+            assert abs(b - case["Bc"]) <= 1e-12 * max(1.0, abs(case["Bc"])), (case["name"], b)
+    # on-boundary case is EXPECT_EQ(Bc, 0.0)
+    a, b = O.safety_cbf_row([0] * 6, [0.8, 0, 0, 0, 0, 0], 0.8)
+    assert b == 0.0
+
+
+def test_double_integrator_one_step(O):
+    # model/tests/DoubleIntegratorXYYawTest.cpp:19-47
+    nxt = O.double_integrator_apply(0.1, [1.0, 2.0, 0.5, 0.1, 0.2, 0.3], [0.5, 0.6, 0.1])
+    exp = [1.0 + 0.1 * 0.1 + 0.5 * 0.5 * 0.01, 2.0 + 0.2 * 0.1 + 0.5 * 0.6 * 0.01,
+           0.5 + 0.3 * 0.1 + 0.5 * 0.1 * 0.01, 0.1 + 0.5 * 0.1, 0.2 + 0.6 * 0.1, 0.3 + 0.1 * 0.1]
+    assert np.allclose(nxt, exp, atol=1e-10, rtol=0)
+
+
+def test_toy_qp(O, gold):
+    # qpcpp/tests/CPLEXTest.cpp:28-56: min x^2+y^2 s.t. x+y>=1 -> OPTIMAL, (0.5, 0.5) +-1e-6
+    g = gold["toy_qp"]
+    r = O.solve_qp(g["P"], g["q"], g["A"], g["l"], g["u"])
+    assert r["status"] == 0
+    assert np.allclose(r["x"], g["x"], atol=g["tol"], rtol=0)
+    assert abs(r["objective"] - 0.5) < 1e-12
+
+
+def test_combinatorics_against_real_reference(O):
+    # math/tests/CombinatoricsTest.cpp + the reference's own Combinatorics.cpp (oracle/_ref)
+    L = O.lib()
+    assert L.oracle_fac(0) == 1 and L.oracle_fac(5) == 120 and L.oracle_fac(20) == 2432902008176640000
+    assert L.oracle_comb(5, 2) == 10 and L.oracle_comb(10, 0) == 1 and L.oracle_perm(5, 2) == 20
+    R = O.ref_lib()
+    if R is None:
+        pytest.skip("oracle/_ref not built (reference tree absent)")
+    import ctypes as C
+    threw = C.c_int()
+    for n in range(0, 21):
+        assert R.ref_fac(n, C.byref(threw)) == L.oracle_fac(n) and threw.value == 0
+        for k in range(0, n + 1):
+            assert R.ref_comb(n, k) == L.oracle_comb(n, k)
+            assert R.ref_perm(n, k) == L.oracle_perm(n, k)
+    R.ref_fac(21, C.byref(threw))
+    assert threw.value == 1  # fac(21) throws in the reference
+
+
+def test_bernstein_closed_forms(O):
+    # SURVEY App. A closed forms of splines/src/detail/BezierOperations.cpp:11-50
+    T = 0.5
+    for t in (0.0, 0.1, 0.30000000000000004, 0.5):
+        s = t / T
+        b0 = [(1 - s) ** 3, 3 * s * (1 - s) ** 2, 3 * s * s * (1 - s), s ** 3]
+        b1 = np.array([-(1 - s) ** 2, (1 - s) * (1 - 3 * s), s * (2 - 3 * s), s * s]) * 3 / T
+        b2 = np.array([1 - s, 3 * s - 2, 1 - 3 * s, s]) * 6 / T ** 2
+        b3 = np.array([-1, 3, -3, 1]) * 6 / T ** 3
+        for d, e in enumerate((b0, b1, b2, b3)):
+            assert np.allclose(O.bernstein_basis(3, T, t, d), e, rtol=1e-13, atol=1e-13)
+    with pytest.raises(RuntimeError):
+        O.bernstein_basis(3, T, 0.6, 0)
+
+
+def test_structure_known_answers(O):
+    # rank(E) = 30 @K16, 6 free dof, reduced-Hessian eigenvalues
+    cfg = O.base_config()
+    st = np.array([[2, 2, 0, 0, 0, 0], [-2, -2, 0, 0, 0, 0]], float)
+    qp = O.build_qp(cfg, st, 0, np.tile([-2, -2, 0], cfg.k_hor))
+    ne = qp["n_eq"]
+    assert ne == 30 and qp["n_cbf"] == 1 and qp["A"].shape == (30 + 1 + 96, 36)
+    E = qp["A"][:ne]
+    assert np.linalg.matrix_rank(E) == 30
+    _, _, vt = np.linalg.svd(E)
+    Z = vt[30:].T
+    w = np.linalg.eigvalsh(Z.T @ qp["P"] @ Z)
+    assert np.allclose(sorted(w), [26.26] * 3 + [986.3] * 3, rtol=2e-3)
+    assert np.linalg.matrix_rank(qp["P"], tol=1e-6) == 27
+    # App. C worked example: CBF row and objective
+    row = qp["A"][ne]
+    U = O.get_table(cfg, "U_basis")
+    assert np.allclose(row, -(8 * U[0] + 8 * U[1]), atol=1e-12)
+    assert qp["u"][ne] == 6611534970880000.0
+    r = O.optimize(cfg, st, 0, np.tile([-2, -2, 0], cfg.k_hor))
+    assert r["success"] and abs(r["objective"][0] + 1378.9905) < 1e-3
+    assert np.allclose(U[:3] @ r["curves"][0], [-270 / 91, -270 / 91, 0], atol=1e-9)
+    assert r["kkt"].max() < 1e-8
