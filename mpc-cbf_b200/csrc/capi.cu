@@ -30,7 +30,7 @@ struct mpccbf_handle {
     int device = -1;
     int sm_count = 0;
     int solver = MPCCBF_SOLVER_REDUCED;
-    int lanes = 32;
+    int lanes = 8;
     cudaStream_t stream = nullptr;
     // device copies of the tables
     double *d_tmpl = nullptr, *d_yw = nullptr, *d_vr = nullptr, *d_kr = nullptr;

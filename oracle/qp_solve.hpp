@@ -130,9 +130,13 @@ int goldfarb_idnani(const Mat<R>& L, const Vec<R>& g, const Mat<R>& C, const Vec
         int p = -1;
         R worst = 0;
         for (int i = 0; i < mi; ++i) {
-            if (is_act[i] || cnorm[i] == 0) continue;
+            if (is_act[i]) continue;
             const R s = dot(C.row(i), w.data(), r) - d[i];
             const R tol = feas_tol * std::max(R(1), std::fabs(d[i]));
+            if (cnorm[i] == 0) {  // 0.w >= d_i: violated for every w (CPLEX presolve: infeasible row)
+                if (s < -tol) return INFEASIBLE;
+                continue;
+            }
             if (s < -tol) {
                 const R v = -s / std::max(cnorm[i], R(1e-300));
                 if (v > worst) { worst = v; p = i; }

@@ -71,3 +71,15 @@ def test_dense_active_cbf_and_infeasible(M, O, emul, N, seed):
     r = check_step(O, oc, O.get_table(oc, "U_basis"), st, tg, got, check_viol_max=16)
     assert got["status"][0, 0, 0] == M.STATUS_INFEASIBLE and got["status"][0, 0, 1] == M.STATUS_SKIPPED
     assert got["iters"].max() > 4  # CBF rows were active somewhere
+
+
+def test_coincident_agents_zero_normal_row(M, O, emul):
+    # two agents at the same xy position: a = (0, 0), b < 0 -> a zero row that no x satisfies.
+    cfg = M.default_config(num_agents=3)
+    st = np.zeros((1, 3, 6)); st[0, 2, :2] = [5.0, 5.0]
+    tg = np.zeros((1, 3, 3)); tg[0, :, 0] = 1.0
+    got = run_emul(M, emul, cfg, st, tg)
+    ref = O.step_batch(O.base_config(num_agents=3), st, tg, prec=1)
+    assert np.array_equal(got["status"], ref["status"])
+    assert list(got["status"][0, 0]) == [M.STATUS_INFEASIBLE, M.STATUS_SKIPPED]
+    assert list(got["status"][0, 2]) == [M.STATUS_OPTIMAL, M.STATUS_OPTIMAL]

@@ -44,9 +44,12 @@ def test_two_agent_swap_shipped_config(M, O, torch_cuda):
         check_step(O, oc, U, st, tg, got, check_viol_max=2)
         # advance (noise-free rollout, MPCCBFFormationControl_example.cpp:191-205)
         for a in range(2):
-            x = got["ctrl_pts"][0, a]
-            st[0, a, :3] = O.eval_curve(oc, x, cfg.h, 0)
-            st[0, a, 3:] = O.eval_curve(oc, x, cfg.h, 1)
+            if got["n_curves"][0, a] > 0:
+                x = got["ctrl_pts"][0, a]
+                st[0, a, :3] = O.eval_curve(oc, x, cfg.h, 0)
+                st[0, a, 3:] = O.eval_curve(oc, x, cfg.h, 1)
+            else:  # MPCCBFFormationControl_example.cpp:208-221: stay in place
+                st[0, a, 3:] = 0.0
     assert abs(h.step_batch_host(np.array([[[2, 2, 0, 0, 0, 0], [-2, -2, 0, 0, 0, 0]]], float),
                                  tg)["objective"][0, 0] + 1378.9905) < 1e-3
     h.close()
