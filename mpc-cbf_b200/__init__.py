@@ -17,7 +17,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmpccbf.so")
+LIB_PATH = os.environ.get("MPCCBF_LIB") or os.path.join(_HERE, "libmpccbf.so")  # override: kernel-variant experiments
 
 OK, ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_ALLOC = 0, -1, -2, -3, -4
 STATUS_OPTIMAL, STATUS_FEASIBLE, STATUS_UNBOUNDED, STATUS_INFEASIBLE = 0, 1, 2, 3

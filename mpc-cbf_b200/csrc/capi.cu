@@ -30,7 +30,7 @@ struct mpccbf_handle {
     int device = -1;
     int sm_count = 0;
     int solver = MPCCBF_SOLVER_REDUCED;
-    int lanes = 8;
+    int lanes = -1;  // lanes per agent-QP: 0 = thread-per-agent kernel, 8/32 = lane-group kernel, -1 = by batch size
     cudaStream_t stream = nullptr;
     // device copies of the tables
     double *d_tmpl = nullptr, *d_yw = nullptr, *d_vr = nullptr, *d_kr = nullptr;
@@ -210,7 +210,13 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
     a.agent_begin = agent_begin;
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
-    CUDA_TRY(launch_impc_reduced(h->dev, a, h->lanes, h->sm_count, stream));
+    int lanes = h->lanes;
+    if (lanes < 0)  // throughput kernel for real batches, lane groups (lower latency) for tiny ones
+        lanes = (a.num_qp >= 32 * h->sm_count) ? 0 : (a.num_qp >= 4 * h->sm_count ? 8 : 32);
+    if (lanes == 0)
+        CUDA_TRY(launch_impc_thread(h->dev, a, h->sm_count, stream));
+    else
+        CUDA_TRY(launch_impc_reduced(h->dev, a, lanes, h->sm_count, stream));
     h->launches += 1;
     h->qps += static_cast<int64_t>(a.num_qp) * h->cfg.impc_iter;
     return MPCCBF_OK;
@@ -262,7 +268,7 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
     h->solver = (cfg->solver == MPCCBF_SOLVER_DENSE || !can_reduce) ? MPCCBF_SOLVER_DENSE : MPCCBF_SOLVER_REDUCED;
     if (const char* env = std::getenv("MPCCBF_LANES")) {
         const int w = std::atoi(env);
-        if (w == 32 || w == 8 || w == 1) h->lanes = w;
+        if (w == 32 || w == 8 || w == 1 || w == 0) h->lanes = w;
     }
     h->device = cfg->device;
     if (cfg->device >= 0) {
@@ -555,7 +561,10 @@ int mpccbf_emul_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t a
     a.agent_begin = agent_begin;
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
-    emul_impc_reduced_host(h->dev, a);
+    if (h->lanes > 0)
+        emul_impc_reduced_host(h->dev, a);
+    else
+        emul_impc_thread_host(h->dev, a);
     return MPCCBF_OK;
 }
 #endif

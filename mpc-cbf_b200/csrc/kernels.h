@@ -33,6 +33,7 @@ struct RolloutConst {
 };
 
 int launch_impc_reduced(const DevTables& T, const StepArgs& a, int width, int sm_count, cudaStream_t stream);
+int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cudaStream_t stream);
 int launch_cbf_rows(const double* states, double* rows, int S, int N, double dmin2, double gamma,
                     int sm_count, cudaStream_t stream);
 int launch_rollout(const double* states, const double* ctrl, const int32_t* n_curves, double* next,
@@ -44,6 +45,7 @@ int dense_qp_solve_host(::mpccbf_handle* h, int32_t batch, int32_t n, int32_t m,
 void set_error(const std::string& msg);
 #ifdef MPCCBF_HOST_EMUL
 void emul_impc_reduced_host(const DevTables& T, const StepArgs& a);
+void emul_impc_thread_host(const DevTables& T, const StepArgs& a);
 #endif
 
 }  // namespace mpccbf

@@ -82,7 +82,8 @@ def test_eight_agent_circle_k20(M, O, torch_cuda):
 
 
 @pytest.mark.parametrize("K,p,N,S", [(20, 4, 16, 64), (16, 3, 2, 128), (10, 2, 8, 64), (40, 8, 4, 32), (20, 4, 64, 4)])
-def test_free_space_swarm(M, O, torch_cuda, K, p, N, S):
+def test_free_space_swarm(M, O, torch_cuda, K, p, N, S, monkeypatch):
+    monkeypatch.setenv("MPCCBF_LANES", "0")
     cfg = north_star_cfg(M, k_hor=K, num_pieces=p, num_agents=N, max_scenarios=S)
     st, tg = swarm(S, N, seed=K * 1000 + N)
     h = M.Handle(cfg)
@@ -92,8 +93,9 @@ def test_free_space_swarm(M, O, torch_cuda, K, p, N, S):
     h.close()
 
 
-@pytest.mark.parametrize("N,seed", [(4, 11), (16, 12), (33, 13)])
-def test_dense_active_cbf_and_infeasible(M, O, torch_cuda, N, seed):
+@pytest.mark.parametrize("N,seed,lanes", [(4, 11, 0), (16, 12, 0), (33, 13, 0), (16, 14, 8), (40, 15, 0)])
+def test_dense_active_cbf_and_infeasible(M, O, torch_cuda, N, seed, lanes, monkeypatch):
+    monkeypatch.setenv("MPCCBF_LANES", str(lanes))  # 0 = thread-per-agent kernel, 8 = lane groups
     S = 32
     cfg = north_star_cfg(M, num_agents=N, max_scenarios=S)
     st, tg = dense_scenarios(S, N, seed, 0.8, spread=1.2, vmax=1.5)
@@ -108,7 +110,7 @@ def test_dense_active_cbf_and_infeasible(M, O, torch_cuda, N, seed):
     h.close()
 
 
-@pytest.mark.parametrize("lanes", [1, 8, 32])
+@pytest.mark.parametrize("lanes", [0, 1, 8, 32])
 def test_lane_widths_agree(M, O, torch_cuda, lanes, monkeypatch):
     monkeypatch.setenv("MPCCBF_LANES", str(lanes))
     cfg = north_star_cfg(M, num_agents=9, max_scenarios=16)
