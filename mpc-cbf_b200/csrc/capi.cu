@@ -455,7 +455,20 @@ int mpccbf_solve_qp_dense(mpccbf_handle* h, int32_t batch, int32_t n, int32_t m,
         return MPCCBF_ERR_INVALID;
     }
     CUDA_TRY(cudaSetDevice(h->device));
-    return dense_qp_solve_host(h, batch, n, m, P, q, A, l, u, lb, ub, x, objective, status, iters);
+    DenseOpts o;
+    o.max_iter = h->cfg.admm_max_iter;
+    o.check_every = h->cfg.admm_check_every;
+    o.eps = h->cfg.admm_eps;
+    o.rho = h->cfg.admm_rho;
+    o.sigma = h->cfg.admm_sigma;
+    o.sm_count = h->sm_count;
+    o.stream = h->stream;
+    rc = dense_qp_solve_host(o, batch, n, m, P, q, A, l, u, lb, ub, x, objective, status, iters);
+    if (rc == MPCCBF_OK) {
+        h->launches += 1;
+        h->qps += batch;
+    }
+    return rc;
 }
 
 int mpccbf_cbf_rows(mpccbf_handle* h, int32_t S, const double* states, double* rows, void* cuda_stream) {

@@ -38,7 +38,13 @@ int launch_cbf_rows(const double* states, double* rows, int S, int N, double dmi
                     int sm_count, cudaStream_t stream);
 int launch_rollout(const double* states, const double* ctrl, const int32_t* n_curves, double* next,
                    int B, const RolloutConst& rc, cudaStream_t stream);
-int dense_qp_solve_host(::mpccbf_handle* h, int32_t batch, int32_t n, int32_t m, const double* P,
+struct DenseOpts {
+    int max_iter, check_every;  // <= 0: defaults (20000, 10)
+    double eps, rho, sigma;     // <= 0: defaults (1e-7, 0.1, 1e-6)
+    int sm_count;
+    cudaStream_t stream;
+};
+int dense_qp_solve_host(const DenseOpts& opts, int32_t batch, int32_t n, int32_t m, const double* P,
                         const double* q, const double* A, const double* l, const double* u,
                         const double* lb, const double* ub, double* x, double* objective,
                         int32_t* status, int32_t* iters);

@@ -367,7 +367,7 @@ QPResult<R> solve_dense_qp(const DenseQP<R>& qp, R feas_tol) {
             if (!cholesky_lower(Lr, chol_tol)) { res.status = ERROR; return res; }
             Vec<R> wk(r, R(0));
             status = ERROR;
-            for (int it = 0; it < 2000; ++it) {
+            for (int it = 0; it < 20000; ++it) {
                 Vec<R> gk(r);
                 for (int i = 0; i < r; ++i) gk[i] = g[i] - rho * wk[i];
                 int it_in = 0;
@@ -381,7 +381,9 @@ QPResult<R> solve_dense_qp(const DenseQP<R>& qp, R feas_tol) {
                 }
                 wk = w;
                 if (wn > R(1e15)) { status = UNBOUNDED; break; }
-                if (dw <= R(1e3) * std::numeric_limits<R>::epsilon() * std::max(R(1), wn)) {
+                // (absolute floor 1e-14: the long-double run of a degenerate slack QP otherwise creeps
+                // for thousands of outer iterations below any tolerance the tests look at)
+                if (dw <= std::max(R(1e3) * std::numeric_limits<R>::epsilon(), R(1e-14)) * std::max(R(1), wn)) {
                     status = OPTIMAL;
                     break;
                 }
