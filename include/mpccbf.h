@@ -175,6 +175,12 @@ int mpccbf_rollout(mpccbf_handle* h, int32_t num_scenarios, const double* states
                    const double* ctrl_pts, const int32_t* n_curves, double* next_states,
                    void* cuda_stream);
 
+/* Same for an agent shard: states / ctrl_pts / n_curves / next_states are indexed
+ * [S][agent_count][...] (the shard's own agents only). */
+int mpccbf_rollout_agents(mpccbf_handle* h, int32_t num_scenarios, int32_t agent_count,
+                          const double* states, const double* ctrl_pts, const int32_t* n_curves,
+                          double* next_states, void* cuda_stream);
+
 /* Agent-sharded control step (one scenario's agents split across GPUs):
  * solves only agents [agent_begin, agent_begin + agent_count) of every scenario. states is the
  * FULL snapshot [S][N][6] (after the all-gather); targets/ctrl_pts/status/n_curves/objective are

@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
     "mpccbf_config_default", "mpccbf_config_validate", "mpccbf_config_from_json", "mpccbf_create",
     "mpccbf_destroy", "mpccbf_last_error", "mpccbf_version", "mpccbf_num_decision_vars",
     "mpccbf_active_solver", "mpccbf_step_batch", "mpccbf_step_batch_host", "mpccbf_optimize_one",
-    "mpccbf_solve_qp_dense", "mpccbf_cbf_rows", "mpccbf_rollout", "mpccbf_step_agents",
+    "mpccbf_solve_qp_dense", "mpccbf_cbf_rows", "mpccbf_rollout", "mpccbf_rollout_agents", "mpccbf_step_agents",
     "mpccbf_last_iteration_counts", "mpccbf_measure_fp64_tflops", "mpccbf_get_table",
     "mpccbf_linear_cost", "mpccbf_get_counters", "mpccbf_host_alloc", "mpccbf_host_free",
 ]
@@ -117,6 +117,7 @@ def lib(path=None):
     L.mpccbf_solve_qp_dense.argtypes = [vp, i32, i32, i32] + [vp] * 11
     L.mpccbf_cbf_rows.argtypes = [vp, i32, vp, vp, vp]
     L.mpccbf_rollout.argtypes = [vp, i32, vp, vp, vp, vp, vp]
+    L.mpccbf_rollout_agents.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp]
     L.mpccbf_last_iteration_counts.argtypes = [vp]
     L.mpccbf_last_iteration_counts.restype = vp
     L.mpccbf_measure_fp64_tflops.argtypes = [vp]
@@ -280,6 +281,10 @@ class Handle:
     def rollout(self, S, states, ctrl_pts, n_curves, next_states, stream=None):
         self._check(self._L.mpccbf_rollout(self._h, S, _ptr(states), _ptr(ctrl_pts), _ptr(n_curves),
                                            _ptr(next_states), stream))
+
+    def rollout_agents(self, S, agent_count, states, ctrl_pts, n_curves, next_states, stream=None):
+        self._check(self._L.mpccbf_rollout_agents(self._h, S, agent_count, _ptr(states), _ptr(ctrl_pts),
+                                                  _ptr(n_curves), _ptr(next_states), stream))
 
     def last_iteration_counts_ptr(self):
         return self._L.mpccbf_last_iteration_counts(self._h)

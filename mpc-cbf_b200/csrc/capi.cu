@@ -170,6 +170,44 @@ int build_device_tables(mpccbf_handle* h) {
             vr[i * K + k] = static_cast<double>(t.Vr(i, k));
             kr[i * K + k] = static_cast<double>(t.Kr(i, k));
         }
+    // ---- polynomial structure of the bound rows along the horizon (see device_tables.h) ---------
+    d.poly = 0;
+    if (K >= 4) {
+        const std::vector<double>& ts = t.h_samples;
+        auto col = [&](int dd, int k, int j) -> xreal { return j < 2 ? t.Ct[dd](k, j) : t.Ot[dd](k, j - 2); };
+        bool ok = true;
+        xreal scale = 0.0L;
+        for (int dd = 1; dd <= 2; ++dd)
+            for (int k = 0; k < K; ++k)
+                for (int j = 0; j < 4; ++j) scale = std::max(scale, std::fabs(col(dd, k, j)));
+        const int ka = 0, kb = K / 2, kc = K - 1;
+        const xreal ta = ts[ka], tb = ts[kb], tc = ts[kc];
+        for (int j = 0; j < 4 && ok; ++j) {
+            // acceleration: affine through the end samples
+            const xreal a0 = col(2, ka, j), a1 = (col(2, kc, j) - col(2, ka, j)) / (tc - ta);
+            for (int k = 0; k < K; ++k)
+                if (std::fabs(a0 + a1 * (ts[k] - ta) - col(2, k, j)) > 1e-12L * scale) ok = false;
+            // velocity: quadratic through three samples (Newton form)
+            const xreal f0 = col(1, ka, j);
+            const xreal f01 = (col(1, kb, j) - f0) / (tb - ta);
+            const xreal f12 = (col(1, kc, j) - col(1, kb, j)) / (tc - tb);
+            const xreal f012 = (f12 - f01) / (tc - ta);
+            for (int k = 0; k < K; ++k) {
+                const xreal tk = ts[k];
+                if (std::fabs(f0 + f01 * (tk - ta) + f012 * (tk - ta) * (tk - tb) - col(1, k, j)) > 1e-12L * scale) ok = false;
+            }
+            // monomial coefficients about t = 0: c2 = f012, c1 = f01 - f012 (ta + tb)
+            d.vq[1][j] = static_cast<double>(f012);
+            d.vq[0][j] = static_cast<double>(f01 - f012 * (ta + tb));
+        }
+        const double step = ts[1] - ts[0];
+        for (int k = 1; k < K && ok; ++k)
+            if (std::fabs((ts[k] - ts[k - 1]) - step) > 1e-9 * step) ok = false;
+        d.inv_h = 1.0 / step;
+        d.poly = ok ? 1 : 0;
+    }
+    if (const char* env = std::getenv("MPCCBF_FULL_SCAN"))
+        if (std::atoi(env) != 0) d.poly = 0;
     if (h->has_device) {
         int rc;
         if ((rc = upload(tmpl, &h->d_tmpl)) != MPCCBF_OK) return rc;
@@ -487,9 +525,19 @@ int mpccbf_cbf_rows(mpccbf_handle* h, int32_t S, const double* states, double* r
 
 int mpccbf_rollout(mpccbf_handle* h, int32_t S, const double* states, const double* ctrl_pts,
                    const int32_t* n_curves, double* next_states, void* cuda_stream) {
+    if (!h) {
+        set_error("handle is NULL");
+        return MPCCBF_ERR_INVALID;
+    }
+    return mpccbf_rollout_agents(h, S, h->cfg.num_agents, states, ctrl_pts, n_curves, next_states, cuda_stream);
+}
+
+int mpccbf_rollout_agents(mpccbf_handle* h, int32_t S, int32_t agent_count, const double* states,
+                          const double* ctrl_pts, const int32_t* n_curves, double* next_states,
+                          void* cuda_stream) {
     int rc = require_device(h);
     if (rc != MPCCBF_OK) return rc;
-    if (S < 0 || !states || !ctrl_pts || !next_states) {
+    if (S < 0 || agent_count < 0 || !states || !ctrl_pts || !next_states) {
         set_error("mpccbf_rollout: invalid argument");
         return MPCCBF_ERR_INVALID;
     }
@@ -498,7 +546,7 @@ int mpccbf_rollout(mpccbf_handle* h, int32_t S, const double* states, const doub
         return MPCCBF_ERR_UNSUPPORTED;
     }
     CUDA_TRY(cudaSetDevice(h->device));
-    CUDA_TRY(launch_rollout(states, ctrl_pts, n_curves, next_states, S * h->cfg.num_agents, h->rc,
+    CUDA_TRY(launch_rollout(states, ctrl_pts, n_curves, next_states, S * agent_count, h->rc,
                             static_cast<cudaStream_t>(cuda_stream)));
     h->launches += 1;
     return MPCCBF_OK;
