@@ -27,6 +27,9 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 METRIC = "mpc_cbf_qps_per_sec"
+# dram__bytes_read.sum + dram__bytes_write.sum of one impc_thread_kernel launch of this workload
+# (ncu --set full, profiles/r1b_impc_thread_ncu_summary.md); None until captured for a new shape
+TRAFFIC_BYTES_PER_LAUNCH = 14.0e6
 UNIT = "QPs/s"
 
 
@@ -299,6 +302,21 @@ def run_b200(args):
     status_np = ho_np["status"]
     counts = {str(k): int(v) for k, v in zip(*np.unique(status_np, return_counts=True))}
     fp64_peak = h.measure_fp64_tflops()
+    # algorithmic FP64 flops of the last timed launch: SURVEY 8d reduced-space formula with the
+    # MEASURED active-set iteration count I of every QP
+    #   F_qp = r^3/3 + m_cbf*8r + m_cbf*r^2 + I*(4*m*r + 2*r^2),  r = 6,  m = 6K + m_cbf
+    b_last = sets[(args.steps - 1 + args.warmup) % R]
+    h.step_batch(S, b_last["states"], d_tg, b_last["ctrl"], b_last["status"], b_last["n_curves"], b_last["objective"], stream=sp)
+    stream.synchronize()
+    gi = h.last_iteration_counts(S * N * iters).reshape(S * N, iters).astype(np.float64)
+    r_dof = 6.0
+    flops = 0.0
+    for it_idx in range(iters):
+        m_cbf = (N - 1) * (1 if it_idx == 0 else cfg.cbf_horizon)
+        m_rows = 6 * K + m_cbf
+        flops += float(np.sum(r_dof ** 3 / 3 + m_cbf * 8 * r_dof + m_cbf * r_dof ** 2
+                              + gi[:, it_idx] * (4 * m_rows * r_dof + 2 * r_dof ** 2)))
+    mean_iters = float(gi.mean())
     if rank != 0:
         h.close()
         return
@@ -312,10 +330,14 @@ def run_b200(args):
         peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
     achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "impc_reduced_kernel", "kernel_ms": kern_ms,
+                "traffic": TRAFFIC_BYTES_PER_LAUNCH if (S, N, K) == (4096, 16, 20) else None, "kernel": "impc_thread_kernel", "kernel_ms": kern_ms,
                 "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
-                "note": "latency/FP64-issue bound by design (<0.5 KB per QP); see DESIGN.md",
-                "fp64_dfma_peak_tflops_measured": fp64_peak}
+                "note": "FP64-issue/latency bound by design (484 B per agent-step); the fp64 entry is the "
+                        "meaningful fraction, see DESIGN.md section 4",
+                "fp64": {"bound": "fp64", "achieved": flops / (kern_ms * 1e-3) / 1e12, "peak": fp64_peak,
+                         "unit": "TFLOP/s", "frac": flops / (kern_ms * 1e-3) / 1e12 / fp64_peak,
+                         "algorithmic_flops_per_launch": flops, "mean_active_set_iterations_per_qp": mean_iters,
+                         "peak_source": "register-resident DFMA loop measured in this run (mpccbf_measure_fp64_tflops)"}}
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:

@@ -193,6 +193,9 @@ int mpccbf_step_agents(mpccbf_handle* h, int32_t num_scenarios, int32_t agent_be
 /* Active-set iteration counts of the last mpccbf_step_batch / _agents call on this handle:
  * iters [S][agents][impc_iter] (device pointer, valid until the next call), for flop accounting. */
 const int32_t* mpccbf_last_iteration_counts(const mpccbf_handle* h);
+/* Copies the first `count` of them to a HOST buffer (synchronises the handle's stream and the
+ * given one is the caller's business: call after the step has completed). */
+int mpccbf_copy_iteration_counts(mpccbf_handle* h, int32_t* out_host, int64_t count);
 
 /* Measures the FP64 FMA throughput of the device with a register-resident DFMA loop (the
  * roofline denominator of the solve kernel). Returns TFLOP/s, or a negative error code. */

@@ -30,7 +30,7 @@ EXPORTED_SYMBOLS = [
     "mpccbf_destroy", "mpccbf_last_error", "mpccbf_version", "mpccbf_num_decision_vars",
     "mpccbf_active_solver", "mpccbf_step_batch", "mpccbf_step_batch_host", "mpccbf_optimize_one",
     "mpccbf_solve_qp_dense", "mpccbf_cbf_rows", "mpccbf_rollout", "mpccbf_rollout_agents", "mpccbf_step_agents",
-    "mpccbf_last_iteration_counts", "mpccbf_measure_fp64_tflops", "mpccbf_get_table",
+    "mpccbf_last_iteration_counts", "mpccbf_copy_iteration_counts", "mpccbf_measure_fp64_tflops", "mpccbf_get_table",
     "mpccbf_linear_cost", "mpccbf_get_counters", "mpccbf_host_alloc", "mpccbf_host_free",
 ]
 
@@ -120,6 +120,7 @@ def lib(path=None):
     L.mpccbf_rollout_agents.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp]
     L.mpccbf_last_iteration_counts.argtypes = [vp]
     L.mpccbf_last_iteration_counts.restype = vp
+    L.mpccbf_copy_iteration_counts.argtypes = [vp, vp, i64]
     L.mpccbf_measure_fp64_tflops.argtypes = [vp]
     L.mpccbf_measure_fp64_tflops.restype = dbl
     L.mpccbf_get_table.argtypes = [vp, C.c_char_p, vp, i64]
@@ -288,6 +289,12 @@ class Handle:
 
     def last_iteration_counts_ptr(self):
         return self._L.mpccbf_last_iteration_counts(self._h)
+
+    def last_iteration_counts(self, count):
+        """Active-set iteration counts [count] (int32) of the last controller step, on the host."""
+        out = np.zeros(count, dtype=np.int32)
+        self._check(self._L.mpccbf_copy_iteration_counts(self._h, out.ctypes.data, count))
+        return out
 
     def measure_fp64_tflops(self):
         v = self._L.mpccbf_measure_fp64_tflops(self._h)

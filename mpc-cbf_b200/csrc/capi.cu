@@ -31,7 +31,7 @@ struct mpccbf_handle {
     int sm_count = 0;
     int solver = MPCCBF_SOLVER_REDUCED;
     int lanes = -1;  // lanes per agent-QP: 0 = thread-per-agent kernel, 8/32 = lane-group kernel, -1 = by batch size
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr;
     // device copies of the tables
     double *d_tmpl = nullptr, *d_yw = nullptr, *d_vr = nullptr, *d_kr = nullptr;
     std::vector<double> h_tmpl, h_yw, h_vr, h_kr;  // host copies (uploaded at create)
@@ -156,7 +156,7 @@ int build_device_tables(mpccbf_handle* h) {
             e[2] = static_cast<double>(t.Ot[dd](k, 0));
             e[3] = static_cast<double>(t.Ot[dd](k, 1));
             e[4] = constant_row ? static_cast<double>(INFINITY) : static_cast<double>(1.0L / nrm);
-            e[5] = 0.0;
+            e[5] = t.h_samples[k];  // sample time t_k (read by the polynomial row scan)
         }
     }
     for (int i = 0; i < t.m1; ++i) {
@@ -184,26 +184,25 @@ int build_device_tables(mpccbf_handle* h) {
         const xreal ta = ts[ka], tb = ts[kb], tc = ts[kc];
         for (int j = 0; j < 4 && ok; ++j) {
             // acceleration: affine through the end samples
-            const xreal a0 = col(2, ka, j), a1 = (col(2, kc, j) - col(2, ka, j)) / (tc - ta);
+            const xreal a1 = (col(2, kc, j) - col(2, ka, j)) / (tc - ta), a0 = col(2, ka, j) - a1 * ta;
             for (int k = 0; k < K; ++k)
-                if (std::fabs(a0 + a1 * (ts[k] - ta) - col(2, k, j)) > 1e-12L * scale) ok = false;
-            // velocity: quadratic through three samples (Newton form)
+                if (std::fabs(a0 + a1 * ts[k] - col(2, k, j)) > 1e-12L * scale) ok = false;
+            // velocity: quadratic through three samples (Newton form -> monomials about t = 0)
             const xreal f0 = col(1, ka, j);
             const xreal f01 = (col(1, kb, j) - f0) / (tb - ta);
             const xreal f12 = (col(1, kc, j) - col(1, kb, j)) / (tc - tb);
             const xreal f012 = (f12 - f01) / (tc - ta);
+            const xreal c2 = f012, c1 = f01 - f012 * (ta + tb), c0 = f0 - f01 * ta + f012 * ta * tb;
             for (int k = 0; k < K; ++k) {
                 const xreal tk = ts[k];
-                if (std::fabs(f0 + f01 * (tk - ta) + f012 * (tk - ta) * (tk - tb) - col(1, k, j)) > 1e-12L * scale) ok = false;
+                if (std::fabs(c0 + (c1 + c2 * tk) * tk - col(1, k, j)) > 1e-12L * scale) ok = false;
             }
-            // monomial coefficients about t = 0: c2 = f012, c1 = f01 - f012 (ta + tb)
-            d.vq[1][j] = static_cast<double>(f012);
-            d.vq[0][j] = static_cast<double>(f01 - f012 * (ta + tb));
+            d.pq[0][j] = static_cast<double>(a0);
+            d.pq[1][j] = static_cast<double>(a1);
+            d.pq[2][j] = static_cast<double>(c0);
+            d.pq[3][j] = static_cast<double>(c1);
+            d.pq[4][j] = static_cast<double>(c2);
         }
-        const double step = ts[1] - ts[0];
-        for (int k = 1; k < K && ok; ++k)
-            if (std::fabs((ts[k] - ts[k - 1]) - step) > 1e-9 * step) ok = false;
-        d.inv_h = 1.0 / step;
         d.poly = ok ? 1 : 0;
     }
     if (const char* env = std::getenv("MPCCBF_FULL_SCAN"))
@@ -251,6 +250,7 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
     int lanes = h->lanes;
     if (lanes < 0)  // throughput kernel for real batches, lane groups (lower latency) for tiny ones
         lanes = (a.num_qp >= 32 * h->sm_count) ? 0 : (a.num_qp >= 4 * h->sm_count ? 8 : 32);
+    if (lanes == 0 && !h->dev.poly) lanes = 8;  // the thread kernel needs the polynomial row structure
     if (lanes == 0)
         CUDA_TRY(launch_impc_thread(h->dev, a, h->sm_count, stream));
     else
@@ -332,7 +332,8 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
         }
         h->sm_count = prop.multiProcessorCount;
         h->has_device = true;
-        if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking) != cudaSuccess) {
             set_error("cudaStreamCreate failed");
             delete h;
             return MPCCBF_ERR_CUDA;
@@ -378,6 +379,7 @@ int mpccbf_destroy(mpccbf_handle* h) {
         for (void* p : ptrs)
             if (p) cudaFree(p);
         if (h->stream) cudaStreamDestroy(h->stream);
+        if (h->stream2) cudaStreamDestroy(h->stream2);
     }
     delete h;
     return MPCCBF_OK;
@@ -430,6 +432,19 @@ int mpccbf_step_batch(mpccbf_handle* h, int32_t S, const double* states, const d
 
 const int32_t* mpccbf_last_iteration_counts(const mpccbf_handle* h) { return h ? h->w_iters : nullptr; }
 
+int mpccbf_copy_iteration_counts(mpccbf_handle* h, int32_t* out_host, int64_t count) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    const int64_t cap = static_cast<int64_t>(h->cfg.max_scenarios) * h->cfg.num_agents * h->cfg.impc_iter;
+    if (!out_host || count < 0 || count > cap) {
+        set_error("mpccbf_copy_iteration_counts: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(cudaMemcpy(out_host, h->w_iters, sizeof(int32_t) * count, cudaMemcpyDeviceToHost));
+    return MPCCBF_OK;
+}
+
 int mpccbf_step_batch_host(mpccbf_handle* h, int32_t S, const double* states, const double* targets,
                            double* ctrl_pts, int32_t* status, int32_t* n_curves, double* objective) {
     int rc = require_device(h);
@@ -440,18 +455,32 @@ int mpccbf_step_batch_host(mpccbf_handle* h, int32_t S, const double* states, co
     }
     if (S == 0) return MPCCBF_OK;
     CUDA_TRY(cudaSetDevice(h->device));
-    const size_t B = static_cast<size_t>(S) * h->cfg.num_agents, n = h->tab.n, it = h->cfg.impc_iter;
-    cudaStream_t st = h->stream;
-    CUDA_TRY(cudaMemcpyAsync(h->w_states, states, sizeof(double) * B * 6, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(h->w_targets, targets, sizeof(double) * B * 3, cudaMemcpyHostToDevice, st));
-    rc = run_step(h, S, 0, h->cfg.num_agents, h->w_states, h->w_targets, 0, h->w_ctrl, nullptr, h->w_status,
-                  h->w_ncurves, h->w_obj, h->w_iters, st);
-    if (rc != MPCCBF_OK) return rc;
-    CUDA_TRY(cudaMemcpyAsync(ctrl_pts, h->w_ctrl, sizeof(double) * B * n, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaMemcpyAsync(status, h->w_status, sizeof(int32_t) * B * it, cudaMemcpyDeviceToHost, st));
-    if (n_curves) CUDA_TRY(cudaMemcpyAsync(n_curves, h->w_ncurves, sizeof(int32_t) * B, cudaMemcpyDeviceToHost, st));
-    if (objective) CUDA_TRY(cudaMemcpyAsync(objective, h->w_obj, sizeof(double) * B, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
+    const size_t N = h->cfg.num_agents, n = h->tab.n, it = h->cfg.impc_iter;
+    // The batch can be cut into scenario chunks that alternate between two streams so that copies
+    // and kernels overlap (MPCCBF_HOST_CHUNKS). Measured on B200 (profiles/r1d_host_chunks.md) this
+    // does NOT pay at 65 536 agents: the fused kernel is latency-bound, a quarter-size launch takes
+    // almost as long as the full one, so the default is one chunk.
+    int nchunks = 1;
+    if (const char* env = std::getenv("MPCCBF_HOST_CHUNKS")) nchunks = std::max(1, std::min(std::atoi(env), S));
+    cudaStream_t streams[2] = {h->stream, h->stream2};
+    for (int c = 0; c < nchunks; ++c) {
+        const int s0 = static_cast<int>(static_cast<int64_t>(S) * c / nchunks);
+        const int s1 = static_cast<int>(static_cast<int64_t>(S) * (c + 1) / nchunks);
+        const size_t a0 = s0 * N, cnt = (s1 - s0) * N;
+        if (cnt == 0) continue;
+        cudaStream_t st = streams[c & 1];
+        CUDA_TRY(cudaMemcpyAsync(h->w_states + a0 * 6, states + a0 * 6, sizeof(double) * cnt * 6, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(h->w_targets + a0 * 3, targets + a0 * 3, sizeof(double) * cnt * 3, cudaMemcpyHostToDevice, st));
+        rc = run_step(h, s1 - s0, 0, h->cfg.num_agents, h->w_states + a0 * 6, h->w_targets + a0 * 3, 0, h->w_ctrl + a0 * n,
+                      nullptr, h->w_status + a0 * it, h->w_ncurves + a0, h->w_obj + a0, h->w_iters + a0 * it, st);
+        if (rc != MPCCBF_OK) return rc;
+        CUDA_TRY(cudaMemcpyAsync(ctrl_pts + a0 * n, h->w_ctrl + a0 * n, sizeof(double) * cnt * n, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(status + a0 * it, h->w_status + a0 * it, sizeof(int32_t) * cnt * it, cudaMemcpyDeviceToHost, st));
+        if (n_curves) CUDA_TRY(cudaMemcpyAsync(n_curves + a0, h->w_ncurves + a0, sizeof(int32_t) * cnt, cudaMemcpyDeviceToHost, st));
+        if (objective) CUDA_TRY(cudaMemcpyAsync(objective + a0, h->w_obj + a0, sizeof(double) * cnt, cudaMemcpyDeviceToHost, st));
+    }
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (nchunks > 1) CUDA_TRY(cudaStreamSynchronize(h->stream2));
     return MPCCBF_OK;
 }
 
@@ -622,7 +651,7 @@ int mpccbf_emul_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t a
     a.agent_begin = agent_begin;
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
-    if (h->lanes > 0)
+    if (h->lanes > 0 || !h->dev.poly)
         emul_impc_reduced_host(h->dev, a);
     else
         emul_impc_thread_host(h->dev, a);

@@ -24,12 +24,12 @@ struct DevTables {
     double Kc[2][2];    // c0 = s'Kc s + target (Kt.s)        (per axis)
     double Kt[2];
     // Single-cubic structure of the reducible case: along the horizon the acceleration rows are
-    // affine and the velocity rows quadratic in the sample time, vel(t) = c0 + c1 t + c2 t^2 with
-    // c_i = vq[i-1][0..1].v + vq[i-1][2..3].[pos; vel]. poly = 1 when the tables verify this to
-    // rounding; the row scan then only visits the samples where an extremum can sit.
+    // affine and the velocity rows quadratic in the sample time t_k,
+    //   acc(t) = p0 + p1 t,   vel(t) = p2 + p3 t + p4 t^2,   p_i = pq[i][0..1].v + pq[i][2..3].[pos; vel].
+    // poly = 1 when the tables verify this to rounding; the row scan then evaluates a row value with
+    // one or two FMAs instead of a 4-term dot product (t_k sits in slot 5 of the acc templates).
     int32_t poly;
-    double vq[2][4];
-    double inv_h;       // 1 / (t_1 - t_0)
+    double pq[5][4];
     const double* tmpl;  // [3][K][kTmplStride]  d = 0 pos, 1 vel, 2 acc
     const double* yw;    // [m1][4]  {Y1(.,0), Y1(.,1), W1(.,0), W1(.,1)}
     const double* Vr;    // [2][K]   general (per-step) reference

@@ -70,6 +70,45 @@ MPCCBF_HD void check_two_sided(double val, double lo, double hi, double inv, dou
     }
 }
 
+// Polynomial row scan of ONE axis (DevTables::poly): acc(t_k) = p0 + p1 t_k, vel(t_k) = p2 + p3 t_k +
+// p4 t_k^2 with p_i linear in this axis' (v, s). The score of a two-sided row is its excess over the
+// feasibility threshold in whitened distance, max(val - (hi + thr), (lo - thr) - val) * inv_norm;
+// positive means violated. hiE / loE are the thresholded bounds (+-inf when there is no bound).
+// A violated row that does not depend on v (inv_norm = inf) scores +inf: infeasible.
+struct AxisPoly {
+    double p[5];
+};
+MPCCBF_HD AxisPoly axis_poly(const double (*pq)[4], double va, double vb, double s0, double s1) {
+    AxisPoly a;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) a.p[i] = fma(pq[i][0], va, fma(pq[i][1], vb, fma(pq[i][2], s0, pq[i][3] * s1)));
+    return a;
+}
+// id_of(dsel, k) gives the row id with the side bit cleared; the side is fixed up by the caller.
+template <class IdOf>
+MPCCBF_HD void scan_axis_poly(const double* tm, int K, const AxisPoly& a, double hiE_acc, double loE_acc, double hiE_vel,
+                              double loE_vel, IdOf id_of, double& best, int& best_id) {
+    const double* ta = tm + 2 * K * kTmplStride;  // acc templates: [4] = inv_norm, [5] = t_k
+    const double* tv = tm + 1 * K * kTmplStride;  // vel templates: [4] = inv_norm
+    for (int k = 0; k < K; ++k) {
+        const double tk = ta[k * kTmplStride + 5];
+        const double acc = fma(a.p[1], tk, a.p[0]);
+        const double vel = fma(fma(a.p[4], tk, a.p[3]), tk, a.p[2]);
+        const double ea = fmax(acc - hiE_acc, loE_acc - acc) * ta[k * kTmplStride + 4];
+        const double ev = fmax(vel - hiE_vel, loE_vel - vel) * tv[k * kTmplStride + 4];
+        if (ea > best) {
+            best = ea;
+            best_id = id_of(0, k);
+        }
+        if (ev > best) {
+            best = ev;
+            best_id = id_of(1, k);
+        }
+    }
+}
+MPCCBF_HD double bound_hi_eff(double hi, double tol) { return fabs(hi) < 1e20 ? hi + tol * fmax(1.0, fabs(hi)) : HUGE_VAL; }
+MPCCBF_HD double bound_lo_eff(double lo, double tol) { return fabs(lo) < 1e20 ? lo - tol * fmax(1.0, fabs(lo)) : -HUGE_VAL; }
+
 // ---- yaw: acceleration and velocity rows of one axis, 2 dof ------------------------------------
 struct RowsAxis {
     const double* tm;  // templates [3][K][kTmplStride]
@@ -77,14 +116,19 @@ struct RowsAxis {
     double s0, s1;       // own pos, vel on this axis
     double lo[2], hi[2]; // [0] acceleration rows, [1] velocity rows
     double tol;
+    const double (*pq)[4];  // non-NULL: polynomial row structure (DevTables::poly)
 
     MPCCBF_HD void scan(const double (&v)[2], double& best, int& best_id) const {
-        for (int k = 0; k < K; ++k) {
-#pragma unroll
-            for (int dsel = 0; dsel < 2; ++dsel) {
+        {   // (the thread kernel requires DevTables::poly; other configurations use the lane-group kernel)
+            const AxisPoly a = axis_poly(pq, v[0], v[1], s0, s1);
+            const int Kc = K;
+            scan_axis_poly(tm, K, a, bound_hi_eff(hi[0], tol), bound_lo_eff(lo[0], tol), bound_hi_eff(hi[1], tol),
+                           bound_lo_eff(lo[1], tol), [Kc](int dsel, int k) { return (dsel * Kc + k) << 1; }, best, best_id);
+            if (best_id >= 0 && best < HUGE_VAL) {  // which side of the winning row is violated
+                const int r = best_id >> 1, dsel = (r >= K) ? 1 : 0, k = r - dsel * K;
                 const double* t = tm + ((2 - dsel) * K + k) * kTmplStride;
                 const double val = fma(t[0], v[0], fma(t[1], v[1], fma(t[2], s0, t[3] * s1)));
-                check_two_sided(val, lo[dsel], hi[dsel], t[4], tol, (dsel * K + k) << 1, best, best_id);
+                if (val - hi[dsel] > lo[dsel] - val) best_id |= 1;
             }
         }
     }
@@ -118,6 +162,7 @@ struct RowsXY {
     int ncbf, hit, self;
     double dmin2, gamma;
     int nid_fix;          // 8K
+    const double (*pq)[4];  // non-NULL: polynomial row structure (DevTables::poly)
 
     MPCCBF_HD void cbf_row(int j, double& ax, double& ay, double& b, int& k) const {
         const int nb = j / hit;
@@ -145,17 +190,24 @@ struct RowsXY {
         }
     }
     MPCCBF_HD void scan(const double (&v)[4], double& best, int& best_id) const {
-        for (int k = 0; k < K; ++k) {
+        {
+            const int Kc = K;
 #pragma unroll
-            for (int dsel = 0; dsel < 2; ++dsel) {
+            for (int ax = 0; ax < 2; ++ax) {
+                const AxisPoly a = axis_poly(pq, v[2 * ax], v[2 * ax + 1], s[ax][0], s[ax][1]);
+                scan_axis_poly(tm, K, a, bound_hi_eff(hi[0][ax], tol), bound_lo_eff(lo[0][ax], tol),
+                               bound_hi_eff(hi[1][ax], tol), bound_lo_eff(lo[1][ax], tol),
+                               [Kc, ax](int dsel, int k) { return ((dsel * Kc + k) * 2 + ax) << 1; }, best, best_id);
+            }
+            if (best_id >= 0 && best < HUGE_VAL) {  // which side of the winning row is violated
+                const int r = best_id >> 1, ax = r & 1, dk = r >> 1, dsel = (dk >= K) ? 1 : 0, k = dk - dsel * K;
                 const double* t = tm + ((2 - dsel) * K + k) * kTmplStride;
-                const double t0 = t[0], t1 = t[1], t2 = t[2], t3 = t[3], inv = t[4];
-#pragma unroll
-                for (int ax = 0; ax < 2; ++ax) {
-                    const double val = fma(t0, v[2 * ax], fma(t1, v[2 * ax + 1], fma(t2, s[ax][0], t3 * s[ax][1])));
-                    check_two_sided(val, lo[dsel][ax], hi[dsel][ax], inv, tol, ((dsel * K + k) * 2 + ax) << 1, best,
-                                    best_id);
-                }
+                const double va = ax ? v[2] : v[0], vb = ax ? v[3] : v[1];
+                const double sa = ax ? s[1][0] : s[0][0], sb = ax ? s[1][1] : s[0][1];
+                const double val = fma(t[0], va, fma(t[1], vb, fma(t[2], sa, t[3] * sb)));
+                const double l = dsel ? (ax ? lo[1][1] : lo[1][0]) : (ax ? lo[0][1] : lo[0][0]);
+                const double h = dsel ? (ax ? hi[1][1] : hi[1][0]) : (ax ? hi[0][1] : hi[0][0]);
+                if (val - h > l - val) best_id |= 1;
             }
         }
         if (ncand < 0) {
@@ -202,6 +254,7 @@ struct RowsXY {
 
 struct AgentCtx {
     const double *tm, *yw, *vr, *kr;  // constant tables (shared memory on the device)
+    const double (*pq)[4];            // polynomial row structure, NULL when DevTables::poly == 0
     const double* st;                 // this agent's scenario states [N][6]
     double* pred;                     // [(k*4 + c) * pstride]
     unsigned short* cand;             // [i * cstride]
@@ -287,6 +340,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         ry.lo[0] = T.lim_lo[0][2]; ry.hi[0] = T.lim_hi[0][2];
         ry.lo[1] = T.lim_lo[1][2]; ry.hi[1] = T.lim_hi[1][2];
         ry.tol = T.feas_tol;
+        ry.pq = c.pq;
         base_status = gi_run<2>(gy, ry, T.max_gi, total_iter);
     }
     // ---- x/y stage A: bound rows only ---------------------------------------------------------
@@ -316,59 +370,83 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     rx.dmin2 = T.dmin2;
     rx.gamma = T.gamma;
     rx.nid_fix = 8 * K;
+    rx.pq = c.pq;
     GIState<4> gx;
     gi_init<4>(gx, v0);
-    if (base_status == MPCCBF_STATUS_OPTIMAL) base_status = gi_run<4>(gx, rx, T.max_gi, total_iter);
 
+    // Phase machine with ONE gi_run<4> call site (the unrolled 4-dof active-set code is the bulk of
+    // the kernel's instruction footprint; inlining it once keeps the kernel inside the instruction
+    // cache):  kStageA -> kIter(0) -> [kReset ->] kIter(1) -> ...
+    enum { kStageA = 0, kReset = 1, kIter = 2 };
     int n_ok = 0;
     bool dirty = false;  // gx has safety rows in its active set (not reusable as stage A)
     double vlast[6] = {0, 0, 0, 0, 0, 0};
     const size_t sbase = static_cast<size_t>(g) * T.iters;
-    for (int it = 0; it < T.iters; ++it) {
+    int mode = kStageA, it = 0, it_iter = 0;
+    bool first_pass = true;
+    while (it < T.iters) {
         int stat = base_status;
-        int it_iter = (it == 0) ? total_iter : 0;
-        if (stat == MPCCBF_STATUS_OPTIMAL) {
-            // ego states the rows are built at: current state (iter 0), else the previous iterate
-            // rolled out to t_k, k < H (ConnectivityIMPCCBF.cpp:135-141,160-175)
-            const int hit = (it == 0) ? 1 : H;
-            if (it == 0) {
-                c.pred[0] = s[0][0];
-                c.pred[c.pstride] = s[1][0];
-                c.pred[2 * c.pstride] = s[0][1];
-                c.pred[3 * c.pstride] = s[1][1];
-            } else {
-                for (int k = 0; k < H; ++k) {
+        bool run = false;
+        if (base_status == MPCCBF_STATUS_OPTIMAL) {
+            if (mode == kIter) {
+                // ego states the rows are built at: current state (iter 0), else the previous iterate
+                // rolled out to t_k, k < H (ConnectivityIMPCCBF.cpp:135-141,160-175)
+                const int hit = (it == 0) ? 1 : H;
+                if (it == 0) {
+                    c.pred[0] = s[0][0];
+                    c.pred[c.pstride] = s[1][0];
+                    c.pred[2 * c.pstride] = s[0][1];
+                    c.pred[3 * c.pstride] = s[1][1];
+                } else if (first_pass) {
+                    for (int k = 0; k < H; ++k) {
 #pragma unroll
-                    for (int d = 0; d < 2; ++d) {
-                        const double* t = c.tm + (d * K + k) * kTmplStride;
+                        for (int d = 0; d < 2; ++d) {
+                            const double* t = c.tm + (d * K + k) * kTmplStride;
 #pragma unroll
-                        for (int ax = 0; ax < 2; ++ax)
-                            c.pred[(k * 4 + d * 2 + ax) * c.pstride] =
-                                fma(t[0], gx.v[2 * ax], fma(t[1], gx.v[2 * ax + 1], fma(t[2], s[ax][0], t[3] * s[ax][1])));
+                            for (int ax = 0; ax < 2; ++ax)
+                                c.pred[(k * 4 + d * 2 + ax) * c.pstride] =
+                                    fma(t[0], gx.v[2 * ax], fma(t[1], gx.v[2 * ax + 1], fma(t[2], s[ax][0], t[3] * s[ax][1])));
+                        }
                     }
                 }
+                if (dirty) {  // back to stage A first (bound rows only), then come back here
+                    mode = kReset;
+                    first_pass = false;
+                } else {
+                    rx.hit = hit;
+                    rx.ncbf = (N - 1) * hit;
+                    build_candidates(rx, T, c.cand, c.cstride);
+                    run = rx.ncand != 0;
+                }
             }
-            if (dirty) {  // back to stage A (bound rows only); always OPTIMAL since it was before
+            if (mode == kReset) {
                 gi_init<4>(gx, v0);
                 rx.ncand = 0;
                 rx.ncbf = 0;
-                int scratch = 0;
-                gi_run<4>(gx, rx, T.max_gi, scratch);
-                it_iter += scratch;
-                dirty = false;
-            }
-            rx.hit = hit;
-            rx.ncbf = (N - 1) * hit;
-            build_candidates(rx, T, c.cand, c.cstride);
-            if (rx.ncand != 0) {
-                int n2 = 0;
-                stat = gi_run<4>(gx, rx, T.max_gi, n2);
-                it_iter += n2;
-                dirty = n2 > 0;
+                run = true;
+            } else if (mode == kStageA) {
+                run = true;
             }
         }
+        int n2 = 0;
+        if (run) stat = gi_run<4>(gx, rx, T.max_gi, n2);
+        it_iter += n2;
+        if (mode == kStageA) {
+            base_status = stat;
+            it_iter += total_iter;  // yaw iterations are booked on IMPC iteration 0
+            mode = kIter;
+            continue;
+        }
+        if (mode == kReset) {  // always OPTIMAL (it was before the safety rows were added)
+            dirty = false;
+            mode = kIter;
+            continue;
+        }
+        dirty = n2 > 0;
+        first_pass = true;
         a.status[sbase + it] = stat;
         if (a.gi_iters) a.gi_iters[sbase + it] = it_iter;
+        it_iter = 0;
         if (stat != MPCCBF_STATUS_OPTIMAL) {
             for (int r = it + 1; r < T.iters; ++r) {
                 a.status[sbase + r] = MPCCBF_STATUS_SKIPPED;
@@ -396,6 +474,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                 out[i] = ctrl_point(c.yw + (piece * T.c + cp) * 4, ax, c.sol);
             }
         }
+        ++it;
     }
     // ---- result record (expanded to control points cooperatively by the warp) ------------------
 #pragma unroll
@@ -424,7 +503,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
 }
 
 struct ThreadSmemLayout {
-    int tm, yw, vr, kr, omap_bytes;  // doubles (omap in bytes), CTA-shared
+    int tm, yw, vr, kr, vq, omap_bytes;  // doubles (omap in bytes), CTA-shared
     int st, pred, sol, cand_bytes;   // per warp: doubles (cand in bytes)
     int nscen_max;
     size_t shared_bytes, warp_bytes;
@@ -436,13 +515,14 @@ static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count) {
     L.yw = T.m1 * 4;
     L.vr = 2 * T.K;
     L.kr = 2 * T.K;
+    L.vq = 20;
     L.omap_bytes = ((T.n * 2 + 15) / 16) * 16;
     L.nscen_max = (32 - 1) / std::max(agent_count, 1) + 2;
     L.st = L.nscen_max * T.N * 6;
     L.pred = std::max(T.H, 1) * 4 * 32;
     L.sol = 32 * kSolStride;
     L.cand_bytes = kCandMax * 32 * 2;
-    L.shared_bytes = sizeof(double) * (L.tm + L.yw + L.vr + L.kr) + L.omap_bytes;
+    L.shared_bytes = sizeof(double) * (L.tm + L.yw + L.vr + L.kr + L.vq) + L.omap_bytes;
     L.warp_bytes = sizeof(double) * (L.st + L.pred + L.sol) + L.cand_bytes;
     return L;
 }
@@ -453,7 +533,8 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
     double* yw = tm + L.tm;
     double* vr = yw + L.yw;
     double* kr = vr + L.vr;
-    unsigned short* omap = reinterpret_cast<unsigned short*>(kr + L.kr);
+    double* svq = kr + L.kr;
+    unsigned short* omap = reinterpret_cast<unsigned short*>(svq + L.vq);
     unsigned char* wbase = smem_raw + L.shared_bytes + static_cast<size_t>(threadIdx.x >> 5) * L.warp_bytes;
     double* wst = reinterpret_cast<double*>(wbase);
     double* wpred = wst + L.st;
@@ -466,6 +547,7 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
         vr[i] = T.Vr[i];
         kr[i] = T.Kr[i];
     }
+    if (threadIdx.x < 20) svq[threadIdx.x] = T.pq[threadIdx.x >> 2][threadIdx.x & 3];
     for (int i = threadIdx.x; i < T.n; i += blockDim.x) {
         const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
         const int ax = rem / T.c, cp = rem - ax * T.c;
@@ -498,6 +580,7 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
             const int self = a.agent_begin + (g - scen * a.agent_count);
             AgentCtx c;
             c.tm = tm; c.yw = yw; c.vr = vr; c.kr = kr;
+            c.pq = T.poly ? reinterpret_cast<const double (*)[4]>(svq) : nullptr;
             c.st = wst + (scen - s_lo) * N * 6;
             c.pred = wpred + lane;
             c.pstride = 32;
@@ -531,6 +614,7 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
         const int self = a.agent_begin + (g - scen * a.agent_count);
         AgentCtx c;
         c.tm = T.tmpl; c.yw = T.yw; c.vr = T.Vr; c.kr = T.Kr;
+        c.pq = T.poly ? T.pq : nullptr;
         c.st = a.states + static_cast<size_t>(scen) * T.N * 6;
         c.pred = pred.data();
         c.pstride = 1;

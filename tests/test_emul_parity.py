@@ -83,3 +83,29 @@ def test_coincident_agents_zero_normal_row(M, O, emul):
     assert np.array_equal(got["status"], ref["status"])
     assert list(got["status"][0, 0]) == [M.STATUS_INFEASIBLE, M.STATUS_SKIPPED]
     assert list(got["status"][0, 2]) == [M.STATUS_OPTIMAL, M.STATUS_OPTIMAL]
+
+
+@pytest.mark.parametrize("K,p", [(20, 4), (16, 3), (40, 8)])
+def test_bound_rows_active_everywhere(M, O, emul, K, p, monkeypatch):
+    # velocities near the limits and far targets: velocity / acceleration rows bind at interior
+    # horizon samples, which exercises the extremum-located row scan (DevTables::poly) against the
+    # oracle, and the same run with the exhaustive scan must give the same answer
+    rng = np.random.default_rng(K)
+    S, N = 40, 4
+    st = np.zeros((S, N, 6))
+    st[:, :, :2] = rng.uniform(-20, 20, size=(S, N, 2)) + 50 * np.arange(N)[None, :, None]
+    st[:, :, 2] = rng.uniform(-1, 1, size=(S, N))
+    st[:, :, 3:5] = rng.uniform(-1.95, 1.95, size=(S, N, 2))
+    st[:, :, 5] = rng.uniform(-2.5, 2.5, size=(S, N))
+    tg = np.zeros((S, N, 3))
+    tg[:, :, :2] = st[:, :, :2] + rng.uniform(-6, 6, size=(S, N, 2))
+    tg[:, :, 2] = rng.uniform(-3, 3, size=(S, N))
+    cfg = M.default_config(k_hor=K, num_pieces=p, d_min=0.8, num_agents=N)
+    got = run_emul(M, emul, cfg, st, tg)
+    oc = O.base_config(k_hor=K, num_pieces=p, d_min=0.8, num_agents=N)
+    check_step(O, oc, O.get_table(oc, "U_basis"), st, tg, got, check_viol_max=4)
+    assert got["iters"].max() >= 3
+    monkeypatch.setenv("MPCCBF_FULL_SCAN", "1")
+    full = run_emul(M, emul, cfg, st, tg)
+    assert np.array_equal(full["status"], got["status"])
+    assert np.abs(full["ctrl_pts"] - got["ctrl_pts"]).max() < 1e-9
