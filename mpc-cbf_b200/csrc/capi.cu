@@ -203,6 +203,11 @@ int build_device_tables(mpccbf_handle* h) {
             d.pq[3][j] = static_cast<double>(c1);
             d.pq[4][j] = static_cast<double>(c2);
         }
+        // the key scan of the thread kernel also needs finite two-sided limits and k < 128
+        for (int dd = 0; dd < 2; ++dd)
+            for (int ax = 0; ax < 3; ++ax)
+                if (!(std::fabs(d.lim_lo[dd][ax]) < 1e20 && std::fabs(d.lim_hi[dd][ax]) < 1e20)) ok = false;
+        if (K > 127) ok = false;
         d.poly = ok ? 1 : 0;
     }
     if (const char* env = std::getenv("MPCCBF_FULL_SCAN"))

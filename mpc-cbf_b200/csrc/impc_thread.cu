@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <vector>
 
 #include "../../include/mpccbf.h"
@@ -84,26 +85,35 @@ MPCCBF_HD AxisPoly axis_poly(const double (*pq)[4], double va, double vb, double
     for (int i = 0; i < 5; ++i) a.p[i] = fma(pq[i][0], va, fma(pq[i][1], vb, fma(pq[i][2], s0, pq[i][3] * s1)));
     return a;
 }
-// id_of(dsel, k) gives the row id with the side bit cleared; the side is fixed up by the caller.
-template <class IdOf>
-MPCCBF_HD void scan_axis_poly(const double* tm, int K, const AxisPoly& a, double hiE_acc, double loE_acc, double hiE_vel,
-                              double loE_vel, IdOf id_of, double& best, int& best_id) {
-    const double* ta = tm + 2 * K * kTmplStride;  // acc templates: [4] = inv_norm, [5] = t_k
-    const double* tv = tm + 1 * K * kTmplStride;  // vel templates: [4] = inv_norm
+// Key scan. With finite two-sided bounds the score of a row is (|val - mid| - half) * inv_norm
+// (mid / half of the thresholded bounds); it only serves to PICK the pivot, so it is compared through
+// the high word of its FP64 pattern (monotone for positive doubles, negative for satisfied rows) with
+// the horizon index packed into the low 7 bits: one integer max per row keeps both the maximum and the
+// arg-max, and the acceleration / velocity families are independent dependency chains. Whether any row
+// is violated is still decided exactly (sign of the score). scn[k] = {t_k, inv_norm_acc, inv_norm_vel,
+// -}; rows that do not depend on v carry inv_norm = 1e300 (violated: key >= kKeyInf, infeasible).
+constexpr int kKeyMask = ~127;
+constexpr int kKeyInf = 0x69000000;  // high word of ~1e200
+#ifdef __CUDA_ARCH__
+#define HIWORD(x) __double2hiint(x)
+#else
+static inline int hiword_host(double x) {
+    long long b;
+    std::memcpy(&b, &x, 8);
+    return static_cast<int>(b >> 32);
+}
+#define HIWORD(x) hiword_host(x)
+#endif
+MPCCBF_HD void scan_axis_keys(const double* scn, int K, const AxisPoly& a, double midA, double halfA, double midV,
+                              double halfV, int& keyA, int& keyV) {
+    const double a0 = a.p[0] - midA, v0 = a.p[2] - midV;
+#pragma unroll 4
     for (int k = 0; k < K; ++k) {
-        const double tk = ta[k * kTmplStride + 5];
-        const double acc = fma(a.p[1], tk, a.p[0]);
-        const double vel = fma(fma(a.p[4], tk, a.p[3]), tk, a.p[2]);
-        const double ea = fmax(acc - hiE_acc, loE_acc - acc) * ta[k * kTmplStride + 4];
-        const double ev = fmax(vel - hiE_vel, loE_vel - vel) * tv[k * kTmplStride + 4];
-        if (ea > best) {
-            best = ea;
-            best_id = id_of(0, k);
-        }
-        if (ev > best) {
-            best = ev;
-            best_id = id_of(1, k);
-        }
+        const double tk = scn[4 * k], ia = scn[4 * k + 1], iv = scn[4 * k + 2];
+        const double sa = (fabs(fma(a.p[1], tk, a0)) - halfA) * ia;
+        const double sv = (fabs(fma(fma(a.p[4], tk, a.p[3]), tk, v0)) - halfV) * iv;
+        keyA = max(keyA, (HIWORD(sa) & kKeyMask) | k);
+        keyV = max(keyV, (HIWORD(sv) & kKeyMask) | k);
     }
 }
 MPCCBF_HD double bound_hi_eff(double hi, double tol) { return fabs(hi) < 1e20 ? hi + tol * fmax(1.0, fabs(hi)) : HUGE_VAL; }
@@ -116,21 +126,23 @@ struct RowsAxis {
     double s0, s1;       // own pos, vel on this axis
     double lo[2], hi[2]; // [0] acceleration rows, [1] velocity rows
     double tol;
-    const double (*pq)[4];  // non-NULL: polynomial row structure (DevTables::poly)
+    const double (*pq)[4];  // polynomial row structure (DevTables::poly)
+    const double* scn;      // [K][4] key-scan table
+    const double* lim;      // {midA, halfA, midV, halfV} of this axis
 
     MPCCBF_HD void scan(const double (&v)[2], double& best, int& best_id) const {
-        {   // (the thread kernel requires DevTables::poly; other configurations use the lane-group kernel)
-            const AxisPoly a = axis_poly(pq, v[0], v[1], s0, s1);
-            const int Kc = K;
-            scan_axis_poly(tm, K, a, bound_hi_eff(hi[0], tol), bound_lo_eff(lo[0], tol), bound_hi_eff(hi[1], tol),
-                           bound_lo_eff(lo[1], tol), [Kc](int dsel, int k) { return (dsel * Kc + k) << 1; }, best, best_id);
-            if (best_id >= 0 && best < HUGE_VAL) {  // which side of the winning row is violated
-                const int r = best_id >> 1, dsel = (r >= K) ? 1 : 0, k = r - dsel * K;
-                const double* t = tm + ((2 - dsel) * K + k) * kTmplStride;
-                const double val = fma(t[0], v[0], fma(t[1], v[1], fma(t[2], s0, t[3] * s1)));
-                if (val - hi[dsel] > lo[dsel] - val) best_id |= 1;
-            }
-        }
+        const AxisPoly a = axis_poly(pq, v[0], v[1], s0, s1);
+        int keyA = 0, keyV = 0;
+        scan_axis_keys(scn, K, a, lim[0], lim[1], lim[2], lim[3], keyA, keyV);
+        const int key = max(keyA, keyV);
+        if (key < 128) return;  // no row violated
+        const int dsel = (keyV > keyA) ? 1 : 0, k = key & 127;
+        best = (key >= kKeyInf) ? HUGE_VAL : 1.0;
+        best_id = (dsel * K + k) << 1;
+        // which side of the winning row is violated
+        const double* t = tm + ((2 - dsel) * K + k) * kTmplStride;
+        const double val = fma(t[0], v[0], fma(t[1], v[1], fma(t[2], s0, t[3] * s1)));
+        if (val - hi[dsel] > lo[dsel] - val) best_id |= 1;
     }
     MPCCBF_HD void normal(int id, double (&np)[2], double& rhs) const {
         const bool up = id & 1;
@@ -162,7 +174,9 @@ struct RowsXY {
     int ncbf, hit, self;
     double dmin2, gamma;
     int nid_fix;          // 8K
-    const double (*pq)[4];  // non-NULL: polynomial row structure (DevTables::poly)
+    const double (*pq)[4];  // polynomial row structure (DevTables::poly)
+    const double* scn;      // [K][4] key-scan table
+    const double* lim;      // [axis x, y]{midA, halfA, midV, halfV}
 
     MPCCBF_HD void cbf_row(int j, double& ax, double& ay, double& b, int& k) const {
         const int nb = j / hit;
@@ -172,7 +186,7 @@ struct RowsXY {
         const double* e = pred + (k * 4) * pstride;
         hocbf_row(e[0], e[pstride], e[2 * pstride], e[3 * pstride], o[0], o[1], o[3], o[4], dmin2, gamma, ax, ay, b);
     }
-    MPCCBF_HD void check_cbf(int j, const double (&v)[4], double& best, int& best_id) const {
+    MPCCBF_HD void check_cbf(int j, const double (&v)[4], int& key, int& jbest) const {
         double ax, ay, b;
         int k;
         cbf_row(j, ax, ay, b, k);
@@ -183,38 +197,47 @@ struct RowsXY {
         if (viol > tol * fmax(1.0, fabs(b)) && fabs(b) < 1e20) {
             const double an2 = fma(ax, ax, ay * ay);
             const double score = (an2 > 0.0) ? viol * t[4] * TRSQRT(an2) : HUGE_VAL;
-            if (score > best) {
-                best = score;
-                best_id = nid_fix + j;
+            const int kk = HIWORD(score) & kKeyMask;
+            if (kk > key) {
+                key = kk;
+                jbest = j;
             }
         }
     }
     MPCCBF_HD void scan(const double (&v)[4], double& best, int& best_id) const {
-        {
-            const int Kc = K;
+        int key[4] = {0, 0, 0, 0};  // [ax * 2 + dsel]
 #pragma unroll
-            for (int ax = 0; ax < 2; ++ax) {
-                const AxisPoly a = axis_poly(pq, v[2 * ax], v[2 * ax + 1], s[ax][0], s[ax][1]);
-                scan_axis_poly(tm, K, a, bound_hi_eff(hi[0][ax], tol), bound_lo_eff(lo[0][ax], tol),
-                               bound_hi_eff(hi[1][ax], tol), bound_lo_eff(lo[1][ax], tol),
-                               [Kc, ax](int dsel, int k) { return ((dsel * Kc + k) * 2 + ax) << 1; }, best, best_id);
-            }
-            if (best_id >= 0 && best < HUGE_VAL) {  // which side of the winning row is violated
-                const int r = best_id >> 1, ax = r & 1, dk = r >> 1, dsel = (dk >= K) ? 1 : 0, k = dk - dsel * K;
-                const double* t = tm + ((2 - dsel) * K + k) * kTmplStride;
-                const double va = ax ? v[2] : v[0], vb = ax ? v[3] : v[1];
-                const double sa = ax ? s[1][0] : s[0][0], sb = ax ? s[1][1] : s[0][1];
-                const double val = fma(t[0], va, fma(t[1], vb, fma(t[2], sa, t[3] * sb)));
-                const double l = dsel ? (ax ? lo[1][1] : lo[1][0]) : (ax ? lo[0][1] : lo[0][0]);
-                const double h = dsel ? (ax ? hi[1][1] : hi[1][0]) : (ax ? hi[0][1] : hi[0][0]);
-                if (val - h > l - val) best_id |= 1;
-            }
+        for (int ax = 0; ax < 2; ++ax) {
+            const AxisPoly a = axis_poly(pq, v[2 * ax], v[2 * ax + 1], s[ax][0], s[ax][1]);
+            scan_axis_keys(scn, K, a, lim[4 * ax], lim[4 * ax + 1], lim[4 * ax + 2], lim[4 * ax + 3], key[2 * ax], key[2 * ax + 1]);
         }
+        int kb = 0, jb = -1;
         if (ncand < 0) {
-            for (int j = 0; j < ncbf; ++j) check_cbf(j, v, best, best_id);
+            for (int j = 0; j < ncbf; ++j) check_cbf(j, v, kb, jb);
         } else {
-            for (int i = 0; i < ncand; ++i) check_cbf(cand[i * cstride], v, best, best_id);
+            for (int i = 0; i < ncand; ++i) check_cbf(cand[i * cstride], v, kb, jb);
         }
+        const int kx = max(key[0], key[1]), ky = max(key[2], key[3]);
+        const int kfix = max(kx, ky);
+        if (kfix < 128 && jb < 0) return;  // feasible
+        if (jb >= 0 && kb >= (kfix & kKeyMask)) {
+            best = (kb >= kKeyInf) ? HUGE_VAL : 1.0;
+            best_id = nid_fix + jb;
+            return;
+        }
+        const int ax = (ky > kx) ? 1 : 0;
+        const int dsel = ax ? ((key[3] > key[2]) ? 1 : 0) : ((key[1] > key[0]) ? 1 : 0);
+        const int k = kfix & 127;
+        best = (kfix >= kKeyInf) ? HUGE_VAL : 1.0;
+        best_id = ((dsel * K + k) * 2 + ax) << 1;
+        // which side of the winning row is violated
+        const double* t = tm + ((2 - dsel) * K + k) * kTmplStride;
+        const double va = ax ? v[2] : v[0], vb = ax ? v[3] : v[1];
+        const double sa = ax ? s[1][0] : s[0][0], sb = ax ? s[1][1] : s[0][1];
+        const double val = fma(t[0], va, fma(t[1], vb, fma(t[2], sa, t[3] * sb)));
+        const double l = dsel ? (ax ? lo[1][1] : lo[1][0]) : (ax ? lo[0][1] : lo[0][0]);
+        const double h = dsel ? (ax ? hi[1][1] : hi[1][0]) : (ax ? hi[0][1] : hi[0][0]);
+        if (val - h > l - val) best_id |= 1;
     }
     MPCCBF_HD void normal(int id, double (&np)[4], double& rhs) const {
         if (id < nid_fix) {
@@ -254,7 +277,9 @@ struct RowsXY {
 
 struct AgentCtx {
     const double *tm, *yw, *vr, *kr;  // constant tables (shared memory on the device)
-    const double (*pq)[4];            // polynomial row structure, NULL when DevTables::poly == 0
+    const double (*pq)[4];            // polynomial row structure (DevTables::poly)
+    const double* scn;                // [K][4] key-scan table {t_k, inv_norm_acc, inv_norm_vel, -}
+    const double* lim;                // [3 axes]{midA, halfA, midV, halfV} of the thresholded bounds
     const double* st;                 // this agent's scenario states [N][6]
     double* pred;                     // [(k*4 + c) * pstride]
     unsigned short* cand;             // [i * cstride]
@@ -341,6 +366,8 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         ry.lo[1] = T.lim_lo[1][2]; ry.hi[1] = T.lim_hi[1][2];
         ry.tol = T.feas_tol;
         ry.pq = c.pq;
+        ry.scn = c.scn;
+        ry.lim = c.lim + 8;
         base_status = gi_run<2>(gy, ry, T.max_gi, total_iter);
     }
     // ---- x/y stage A: bound rows only ---------------------------------------------------------
@@ -371,19 +398,25 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     rx.gamma = T.gamma;
     rx.nid_fix = 8 * K;
     rx.pq = c.pq;
+    rx.scn = c.scn;
+    rx.lim = c.lim;
     GIState<4> gx;
     gi_init<4>(gx, v0);
+    GIState<4> snap;  // stage-A factorisation; its address escapes so that it lives in local memory
+#ifdef __CUDA_ARCH__
+    asm volatile("" ::"l"(&snap) : "memory");
+#endif
 
     // Phase machine with ONE gi_run<4> call site (the unrolled 4-dof active-set code is the bulk of
     // the kernel's instruction footprint; inlining it once keeps the kernel inside the instruction
-    // cache):  kStageA -> kIter(0) -> [kReset ->] kIter(1) -> ...
-    enum { kStageA = 0, kReset = 1, kIter = 2 };
+    // cache):  kStageA -> kIter(0) -> kIter(1) -> ...   Before an iteration whose predecessor put
+    // safety rows into the active set, the stage-A factorisation is restored from `snap`.
+    enum { kStageA = 0, kIter = 2 };
     int n_ok = 0;
     bool dirty = false;  // gx has safety rows in its active set (not reusable as stage A)
     double vlast[6] = {0, 0, 0, 0, 0, 0};
     const size_t sbase = static_cast<size_t>(g) * T.iters;
     int mode = kStageA, it = 0, it_iter = 0;
-    bool first_pass = true;
     while (it < T.iters) {
         int stat = base_status;
         bool run = false;
@@ -397,7 +430,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                     c.pred[c.pstride] = s[1][0];
                     c.pred[2 * c.pstride] = s[0][1];
                     c.pred[3 * c.pstride] = s[1][1];
-                } else if (first_pass) {
+                } else {
                     for (int k = 0; k < H; ++k) {
 #pragma unroll
                         for (int d = 0; d < 2; ++d) {
@@ -409,22 +442,13 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                         }
                     }
                 }
-                if (dirty) {  // back to stage A first (bound rows only), then come back here
-                    mode = kReset;
-                    first_pass = false;
-                } else {
-                    rx.hit = hit;
-                    rx.ncbf = (N - 1) * hit;
-                    build_candidates(rx, T, c.cand, c.cstride);
-                    run = rx.ncand != 0;
-                }
-            }
-            if (mode == kReset) {
-                gi_init<4>(gx, v0);
-                rx.ncand = 0;
-                rx.ncbf = 0;
-                run = true;
-            } else if (mode == kStageA) {
+                if (dirty) gx = snap;
+                dirty = false;
+                rx.hit = hit;
+                rx.ncbf = (N - 1) * hit;
+                build_candidates(rx, T, c.cand, c.cstride);
+                run = rx.ncand != 0;
+            } else {
                 run = true;
             }
         }
@@ -434,16 +458,11 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         if (mode == kStageA) {
             base_status = stat;
             it_iter += total_iter;  // yaw iterations are booked on IMPC iteration 0
-            mode = kIter;
-            continue;
-        }
-        if (mode == kReset) {  // always OPTIMAL (it was before the safety rows were added)
-            dirty = false;
+            snap = gx;
             mode = kIter;
             continue;
         }
         dirty = n2 > 0;
-        first_pass = true;
         a.status[sbase + it] = stat;
         if (a.gi_iters) a.gi_iters[sbase + it] = it_iter;
         it_iter = 0;
@@ -502,6 +521,23 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     }
 }
 
+// lim[axis] = {midA, halfA, midV, halfV} of the thresholded bounds; scn[k] = {t_k, inv_norm of the
+// acceleration row, inv_norm of the velocity row, 0} with 1e300 standing for "row independent of v"
+__host__ __device__ inline void fill_scan_tables(const DevTables& T, const double* tm, double* lim, double* scn, int tid, int nthr) {
+    for (int i = tid; i < 6; i += nthr) {
+        const int axis = i >> 1, dsel = i & 1;
+        const double hi = bound_hi_eff(T.lim_hi[dsel][axis], T.feas_tol), lo = bound_lo_eff(T.lim_lo[dsel][axis], T.feas_tol);
+        lim[axis * 4 + dsel * 2 + 0] = 0.5 * (hi + lo);
+        lim[axis * 4 + dsel * 2 + 1] = 0.5 * (hi - lo);
+    }
+    for (int k = tid; k < T.K; k += nthr) {
+        scn[4 * k + 0] = tm[(2 * T.K + k) * kTmplStride + 5];
+        scn[4 * k + 1] = fmin(tm[(2 * T.K + k) * kTmplStride + 4], 1e300);
+        scn[4 * k + 2] = fmin(tm[(1 * T.K + k) * kTmplStride + 4], 1e300);
+        scn[4 * k + 3] = 0.0;
+    }
+}
+
 struct ThreadSmemLayout {
     int tm, yw, vr, kr, vq, omap_bytes;  // doubles (omap in bytes), CTA-shared
     int st, pred, sol, cand_bytes;   // per warp: doubles (cand in bytes)
@@ -515,7 +551,7 @@ static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count) {
     L.yw = T.m1 * 4;
     L.vr = 2 * T.K;
     L.kr = 2 * T.K;
-    L.vq = 20;
+    L.vq = 20 + 12 + 4 * T.K;  // pq, lim[3][4], scn[K][4]
     L.omap_bytes = ((T.n * 2 + 15) / 16) * 16;
     L.nscen_max = (32 - 1) / std::max(agent_count, 1) + 2;
     L.st = L.nscen_max * T.N * 6;
@@ -548,6 +584,7 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
         kr[i] = T.Kr[i];
     }
     if (threadIdx.x < 20) svq[threadIdx.x] = T.pq[threadIdx.x >> 2][threadIdx.x & 3];
+    fill_scan_tables(T, tm, svq + 20, svq + 32, threadIdx.x, blockDim.x);
     for (int i = threadIdx.x; i < T.n; i += blockDim.x) {
         const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
         const int ax = rem / T.c, cp = rem - ax * T.c;
@@ -580,7 +617,9 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
             const int self = a.agent_begin + (g - scen * a.agent_count);
             AgentCtx c;
             c.tm = tm; c.yw = yw; c.vr = vr; c.kr = kr;
-            c.pq = T.poly ? reinterpret_cast<const double (*)[4]>(svq) : nullptr;
+            c.pq = reinterpret_cast<const double (*)[4]>(svq);
+            c.lim = svq + 20;
+            c.scn = svq + 32;
             c.st = wst + (scen - s_lo) * N * 6;
             c.pred = wpred + lane;
             c.pstride = 32;
@@ -609,12 +648,16 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
 void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
     std::vector<double> pred(static_cast<size_t>(std::max(T.H, 1)) * 4), sol(kSolStride);
     std::vector<unsigned short> cand(kCandMax);
+    std::vector<double> lim(12), scn(static_cast<size_t>(4) * T.K);
+    fill_scan_tables(T, T.tmpl, lim.data(), scn.data(), 0, 1);
     for (int g = 0; g < a.num_qp; ++g) {
         const int scen = g / a.agent_count;
         const int self = a.agent_begin + (g - scen * a.agent_count);
         AgentCtx c;
         c.tm = T.tmpl; c.yw = T.yw; c.vr = T.Vr; c.kr = T.Kr;
-        c.pq = T.poly ? T.pq : nullptr;
+        c.pq = T.pq;
+        c.lim = lim.data();
+        c.scn = scn.data();
         c.st = a.states + static_cast<size_t>(scen) * T.N * 6;
         c.pred = pred.data();
         c.pstride = 1;
