@@ -461,10 +461,24 @@ int mpccbf_step_batch_host(mpccbf_handle* h, int32_t S, const double* states, co
     if (S == 0) return MPCCBF_OK;
     CUDA_TRY(cudaSetDevice(h->device));
     const size_t N = h->cfg.num_agents, n = h->tab.n, it = h->cfg.impc_iter;
-    // The batch can be cut into scenario chunks that alternate between two streams so that copies
-    // and kernels overlap (MPCCBF_HOST_CHUNKS). Measured on B200 (profiles/r1d_host_chunks.md) this
-    // does NOT pay at 65 536 agents: the fused kernel is latency-bound, a quarter-size launch takes
-    // almost as long as the full one, so the default is one chunk.
+    // Control points are 384 of the 404 output bytes per agent. When the caller's ctrl_pts buffer is
+    // pinned host memory (mpccbf_host_alloc, cudaHostAlloc / cudaHostRegister: mapped under UVA) the
+    // kernel stores them straight into it — coalesced posted writes over PCIe that overlap the solve —
+    // instead of writing HBM and copying afterwards. The small per-agent outputs (status, n_curves,
+    // objective) are single 4/8-byte stores and stay on the copy path. MPCCBF_ZEROCOPY=0 disables it.
+    double* ctrl_dev = nullptr;
+    {
+        static const bool allow = [] { const char* e = std::getenv("MPCCBF_ZEROCOPY"); return !e || std::atoi(e) != 0; }();
+        cudaPointerAttributes pa;
+        if (allow && cudaPointerGetAttributes(&pa, ctrl_pts) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer)
+            ctrl_dev = static_cast<double*>(pa.devicePointer);
+        else
+            (void)cudaGetLastError();
+    }
+    // The batch can also be cut into scenario chunks that alternate between two streams so that
+    // copies and kernels overlap (MPCCBF_HOST_CHUNKS). Measured on B200 (profiles/r1d_host_chunks.md)
+    // this does NOT pay at 65 536 agents: the fused kernel is latency-bound, a quarter-size launch
+    // takes almost as long as the full one, so the default is one chunk.
     int nchunks = 1;
     if (const char* env = std::getenv("MPCCBF_HOST_CHUNKS")) nchunks = std::max(1, std::min(std::atoi(env), S));
     cudaStream_t streams[2] = {h->stream, h->stream2};
@@ -476,10 +490,12 @@ int mpccbf_step_batch_host(mpccbf_handle* h, int32_t S, const double* states, co
         cudaStream_t st = streams[c & 1];
         CUDA_TRY(cudaMemcpyAsync(h->w_states + a0 * 6, states + a0 * 6, sizeof(double) * cnt * 6, cudaMemcpyHostToDevice, st));
         CUDA_TRY(cudaMemcpyAsync(h->w_targets + a0 * 3, targets + a0 * 3, sizeof(double) * cnt * 3, cudaMemcpyHostToDevice, st));
-        rc = run_step(h, s1 - s0, 0, h->cfg.num_agents, h->w_states + a0 * 6, h->w_targets + a0 * 3, 0, h->w_ctrl + a0 * n,
+        double* ctrl_out = ctrl_dev ? ctrl_dev + a0 * n : h->w_ctrl + a0 * n;
+        rc = run_step(h, s1 - s0, 0, h->cfg.num_agents, h->w_states + a0 * 6, h->w_targets + a0 * 3, 0, ctrl_out,
                       nullptr, h->w_status + a0 * it, h->w_ncurves + a0, h->w_obj + a0, h->w_iters + a0 * it, st);
         if (rc != MPCCBF_OK) return rc;
-        CUDA_TRY(cudaMemcpyAsync(ctrl_pts + a0 * n, h->w_ctrl + a0 * n, sizeof(double) * cnt * n, cudaMemcpyDeviceToHost, st));
+        if (!ctrl_dev)
+            CUDA_TRY(cudaMemcpyAsync(ctrl_pts + a0 * n, h->w_ctrl + a0 * n, sizeof(double) * cnt * n, cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaMemcpyAsync(status + a0 * it, h->w_status + a0 * it, sizeof(int32_t) * cnt * it, cudaMemcpyDeviceToHost, st));
         if (n_curves) CUDA_TRY(cudaMemcpyAsync(n_curves + a0, h->w_ncurves + a0, sizeof(int32_t) * cnt, cudaMemcpyDeviceToHost, st));
         if (objective) CUDA_TRY(cudaMemcpyAsync(objective + a0, h->w_obj + a0, sizeof(double) * cnt, cudaMemcpyDeviceToHost, st));

@@ -148,7 +148,7 @@ __host__ __device__ int gi_run(GIState<D>& g, const Rows& rows, int max_iter, in
                 for (int col = 0; col < D; ++col)
                     if (col == g.q) {
 #pragma unroll
-                        for (int i = 0; i < D; ++i) g.Rm[i][col] = (i <= col) ? d[i] : 0.0;
+                        for (int i = 0; i <= col; ++i) g.Rm[i][col] = d[i];
                         g.u[col] = up_mult;
                     }
                 ++g.q;
@@ -159,11 +159,9 @@ __host__ __device__ int gi_run(GIState<D>& g, const Rows& rows, int max_iter, in
             for (int col = 0; col < D - 1; ++col)
                 if (col >= lpos) {
 #pragma unroll
-                    for (int i = 0; i < D; ++i) g.Rm[i][col] = g.Rm[i][col + 1];
+                    for (int i = 0; i <= col + 1; ++i) g.Rm[i][col] = g.Rm[i][col + 1];  // Hessenberg part
                     g.u[col] = g.u[col + 1];
                 }
-#pragma unroll
-            for (int i = 0; i < D; ++i) g.Rm[i][D - 1] = 0.0;
             g.u[D - 1] = 0.0;
             --g.q;
 #pragma unroll
@@ -177,9 +175,10 @@ __host__ __device__ int gi_run(GIState<D>& g, const Rows& rows, int max_iter, in
 #pragma unroll
                         for (int col = 0; col < D; ++col)
                             if (col >= k) {
-                                const double a1 = g.Rm[k][col], a2 = g.Rm[k + 1][col];
+                                // (the sub-diagonal entry b is annihilated; it is never read again)
+                                const double a1 = g.Rm[k][col], a2 = (col > k) ? g.Rm[k + 1][col] : b;
                                 g.Rm[k][col] = fma(cs, a1, sn * a2);
-                                g.Rm[k + 1][col] = fma(-sn, a1, cs * a2);
+                                if (col > k) g.Rm[k + 1][col] = fma(-sn, a1, cs * a2);
                             }
 #pragma unroll
                         for (int i = 0; i < D; ++i) {

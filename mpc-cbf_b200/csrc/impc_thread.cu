@@ -116,6 +116,24 @@ MPCCBF_HD void scan_axis_keys(const double* scn, int K, const AxisPoly& a, doubl
         keyV = max(keyV, (HIWORD(sv) & kKeyMask) | k);
     }
 }
+// both x/y axes in one pass over k: four independent chains, one load of scn[k]
+MPCCBF_HD void scan_axes_keys2(const double* scn, int K, const AxisPoly& ax, const AxisPoly& ay, const double* lim, int (&key)[4]) {
+    const double xa0 = ax.p[0] - lim[0], xv0 = ax.p[2] - lim[2];
+    const double ya0 = ay.p[0] - lim[4], yv0 = ay.p[2] - lim[6];
+    const double hxa = lim[1], hxv = lim[3], hya = lim[5], hyv = lim[7];
+#pragma unroll 2
+    for (int k = 0; k < K; ++k) {
+        const double tk = scn[4 * k], ia = scn[4 * k + 1], iv = scn[4 * k + 2];
+        const double s0 = (fabs(fma(ax.p[1], tk, xa0)) - hxa) * ia;
+        const double s1 = (fabs(fma(fma(ax.p[4], tk, ax.p[3]), tk, xv0)) - hxv) * iv;
+        const double s2 = (fabs(fma(ay.p[1], tk, ya0)) - hya) * ia;
+        const double s3 = (fabs(fma(fma(ay.p[4], tk, ay.p[3]), tk, yv0)) - hyv) * iv;
+        key[0] = max(key[0], (HIWORD(s0) & kKeyMask) | k);
+        key[1] = max(key[1], (HIWORD(s1) & kKeyMask) | k);
+        key[2] = max(key[2], (HIWORD(s2) & kKeyMask) | k);
+        key[3] = max(key[3], (HIWORD(s3) & kKeyMask) | k);
+    }
+}
 MPCCBF_HD double bound_hi_eff(double hi, double tol) { return fabs(hi) < 1e20 ? hi + tol * fmax(1.0, fabs(hi)) : HUGE_VAL; }
 MPCCBF_HD double bound_lo_eff(double lo, double tol) { return fabs(lo) < 1e20 ? lo - tol * fmax(1.0, fabs(lo)) : -HUGE_VAL; }
 
@@ -206,10 +224,10 @@ struct RowsXY {
     }
     MPCCBF_HD void scan(const double (&v)[4], double& best, int& best_id) const {
         int key[4] = {0, 0, 0, 0};  // [ax * 2 + dsel]
-#pragma unroll
-        for (int ax = 0; ax < 2; ++ax) {
-            const AxisPoly a = axis_poly(pq, v[2 * ax], v[2 * ax + 1], s[ax][0], s[ax][1]);
-            scan_axis_keys(scn, K, a, lim[4 * ax], lim[4 * ax + 1], lim[4 * ax + 2], lim[4 * ax + 3], key[2 * ax], key[2 * ax + 1]);
+        {
+            const AxisPoly px = axis_poly(pq, v[0], v[1], s[0][0], s[0][1]);
+            const AxisPoly py = axis_poly(pq, v[2], v[3], s[1][0], s[1][1]);
+            scan_axes_keys2(scn, K, px, py, lim, key);
         }
         int kb = 0, jb = -1;
         if (ncand < 0) {

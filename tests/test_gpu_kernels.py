@@ -92,6 +92,14 @@ def test_device_pointer_step_rollout_and_agent_shards(M, O, torch):
     host = h.step_batch_host(st, tg)
     assert np.array_equal(cp.cpu().numpy(), host["ctrl_pts"])  # same kernel, same bits
     assert np.array_equal(status.cpu().numpy(), host["status"])
+    # pinned output buffers: control points are stored by the kernel straight into host memory
+    pinned = dict(ctrl_pts=torch.full((S, N, h.n), np.nan, dtype=torch.float64).pin_memory(),
+                  status=torch.zeros((S, N, 2), dtype=torch.int32).pin_memory(),
+                  n_curves=torch.zeros((S, N), dtype=torch.int32).pin_memory(),
+                  objective=torch.zeros((S, N), dtype=torch.float64).pin_memory())
+    h.step_batch_host(st, tg, out={k: v.numpy() for k, v in pinned.items()})
+    for k in pinned:
+        assert np.array_equal(pinned[k].numpy(), host[k]), k
     # agent-sharded launch: two halves reproduce the whole
     for begin, cnt in ((0, 8), (8, 8), (5, 3)):
         cp2 = torch.zeros((S, cnt, h.n), dtype=torch.float64, device="cuda")
