@@ -6,6 +6,7 @@
 #include <cstring>
 #include <thread>
 
+#include "cbf_filter.hpp"
 #include "mpc_cbf.hpp"
 
 using namespace oracle;
@@ -280,6 +281,77 @@ int oracle_eval_curve(const mpccbf_config* cfg, const double* ctrl_pts, double t
 }
 
 const char* oracle_last_error() { return g_err.c_str(); }
+
+// ---- CBF-only filter (cbf::ConnectivityControl) -------------------------------
+// lambda2 + normalised Fiedler vector of one scenario's positions (states [N][6]).
+double oracle_lambda2(const double* states, int N, double dmax, int prec, double* fiedler) {
+    auto run = [&](auto tag) -> double {
+        using R = decltype(tag);
+        std::vector<R> st(6 * N);
+        for (int i = 0; i < 6 * N; ++i) st[i] = R(states[i]);
+        Vec<R> fv;
+        const R l2 = lambda2<R>(st.data(), N, R(dmax), fv);
+        if (fiedler) to_double(fv, fiedler);
+        return static_cast<double>(l2);
+    };
+    return prec ? run((long double)0) : run((double)0);
+}
+
+// Connectivity HOCBF row of agent `self`: Ac [3], *Bc  (Ac.u + Bc >= 0), *lam2.
+void oracle_conn_cbf_row(const double* states, int N, int self, double dmax, double gamma, int prec,
+                         double* Ac, double* Bc, double* lam2) {
+    auto run = [&](auto tag) {
+        using R = decltype(tag);
+        std::vector<R> st(6 * N);
+        for (int i = 0; i < 6 * N; ++i) st[i] = R(states[i]);
+        Vec<R> fv;
+        const R l2 = lambda2<R>(st.data(), N, R(dmax), fv);
+        R a[3], b;
+        conn_cbf_row<R>(st.data(), N, self, fv, l2, R(dmax), R(gamma), R(0.1), a, b);
+        for (int i = 0; i < 3; ++i) Ac[i] = static_cast<double>(a[i]);
+        *Bc = static_cast<double>(b);
+        if (lam2) *lam2 = static_cast<double>(l2);
+    };
+    if (prec) run((long double)0);
+    else run((double)0);
+}
+
+// Distance CLF row: Ac [3], *Bc  (Ac.u <= -Bc).
+void oracle_clf_row(const double* ego, const double* nbr, double* Ac, double* Bc) {
+    long double e[6], n[6], a[3], b;
+    for (int i = 0; i < 6; ++i) { e[i] = ego[i]; n[i] = nbr[i]; }
+    clf_row<long double>(e, n, a, b);
+    for (int i = 0; i < 3; ++i) Ac[i] = static_cast<double>(a[i]);
+    *Bc = static_cast<double>(b);
+}
+
+// ConnectivityControl::optimize for every agent of every scenario (Jacobi: one snapshot).
+// states [S][N][6], desired_u [S][N][3] -> u [S][N][3] (zeros unless OPTIMAL), status [S][N],
+// lambda2 [S] (may be NULL).
+int oracle_cbf_filter_batch(const mpccbf_config* cfg, int S, const double* states, const double* desired_u,
+                            double feas_tol, int prec, double* u, int32_t* status, double* lam2) {
+    try {
+        const int N = cfg->num_agents;
+        auto run = [&](auto tag) {
+            using R = decltype(tag);
+            std::vector<R> st(6 * N);
+            for (int s = 0; s < S; ++s) {
+                for (int i = 0; i < 6 * N; ++i) st[i] = R(states[static_cast<size_t>(s) * 6 * N + i]);
+                for (int a = 0; a < N; ++a) {
+                    const size_t g = static_cast<size_t>(s) * N + a;
+                    const R du[3] = {R(desired_u[3 * g]), R(desired_u[3 * g + 1]), R(desired_u[3 * g + 2])};
+                    auto r = cbf_filter<R>(*cfg, st.data(), N, a, du, R(feas_tol));
+                    status[g] = r.status;
+                    for (int j = 0; j < 3; ++j) u[3 * g + j] = static_cast<double>(r.u[j]);
+                    if (lam2 && a == 0) lam2[s] = static_cast<double>(r.lambda2);
+                }
+            }
+        };
+        if (prec) run((long double)0);
+        else run((double)0);
+    } ORACLE_CATCH(-1)
+    return 0;
+}
 
 int oracle_hardware_threads() { return static_cast<int>(std::thread::hardware_concurrency()); }
 

@@ -252,3 +252,50 @@ def eval_curve(cfg, ctrl_pts, t, d):
 
 def hardware_threads():
     return int(lib().oracle_hardware_threads())
+
+
+# ---- CBF-only filter (cbf::ConnectivityControl) ------------------------------------------------------
+def _vp(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def lambda2(states, dmax, prec=1):
+    """ConnectivityCBF::getLambda2 for one scenario: (lambda2, normalised Fiedler vector)."""
+    states = _arr(states)
+    N = states.shape[0]
+    fv = np.zeros(N)
+    f = lib().oracle_lambda2
+    f.restype = C.c_double
+    l2 = f(_vp(states), C.c_int(N), C.c_double(dmax), C.c_int(prec), _vp(fv))
+    return l2, fv
+
+
+def conn_cbf_row(states, self_idx, dmax, gamma=5.0, prec=1):
+    """Connectivity HOCBF row of one agent: (Ac [3], Bc, lambda2) with Ac.u + Bc >= 0."""
+    states = _arr(states)
+    Ac = np.zeros(3); Bc = C.c_double(); l2 = C.c_double()
+    lib().oracle_conn_cbf_row(_vp(states), C.c_int(states.shape[0]), C.c_int(self_idx), C.c_double(dmax),
+                              C.c_double(gamma), C.c_int(prec), _vp(Ac), C.byref(Bc), C.byref(l2))
+    return Ac, Bc.value, l2.value
+
+
+def clf_row(ego, nbr):
+    """Distance CLF row: (Ac [3], Bc) with Ac.u <= -Bc."""
+    ego, nbr = _arr(ego), _arr(nbr)
+    Ac = np.zeros(3); Bc = C.c_double()
+    lib().oracle_clf_row(_vp(ego), _vp(nbr), _vp(Ac), C.byref(Bc))
+    return Ac, Bc.value
+
+
+def cbf_filter_batch(cfg, states, desired_u, feas_tol=1e-9, prec=1):
+    """ConnectivityControl::optimize for every agent: states [S][N][6], desired_u [S][N][3]."""
+    states, desired_u = _arr(states), _arr(desired_u)
+    S, N = states.shape[:2]
+    c2 = Config.from_buffer_copy(cfg)
+    c2.num_agents = N
+    u = np.zeros((S, N, 3)); status = np.zeros((S, N), dtype=np.int32); l2 = np.zeros(S)
+    rc = lib().oracle_cbf_filter_batch(C.byref(c2), C.c_int(S), _vp(states), _vp(desired_u), C.c_double(feas_tol),
+                                       C.c_int(prec), _vp(u), _vp(status), _vp(l2))
+    if rc != 0:
+        raise RuntimeError("oracle_cbf_filter_batch failed: " + lib().oracle_last_error().decode())
+    return dict(u=u, status=status, lambda2=l2)

@@ -28,6 +28,53 @@ def test_safety_cbf_goldens(O, gold):
     assert b == 0.0
 
 
+def test_connectivity_cbf_goldens(O, gold):
+    # cbf/tests/TestInitConnectivity.cpp:103-153: EXPECT_NEAR(Ac, 1e-6), EXPECT_DOUBLE_EQ(Bc) (4 ulp)
+    g = gold["connectivity_cbf"]
+    for case in g["cases"]:
+        for prec in (0, 1):
+            Ac, Bc, l2 = O.conn_cbf_row(case["states"], case["self"], g["dmax"], g["gamma"], prec=prec)
+            assert np.allclose(Ac, case["Ac"], atol=g["tol_Ac"], rtol=0), case["name"]
+            assert abs(Bc - case["Bc"]) <= 8 * np.spacing(abs(case["Bc"])), (case["name"], Bc)
+            assert l2 > 0
+    # lambda2 of the oracle's Jacobi solver against LAPACK on random swarms
+    rng = np.random.default_rng(3)
+    for N in (2, 5, 16):
+        st = np.zeros((N, 6))
+        st[:, :2] = rng.uniform(-2.5, 2.5, size=(N, 2))
+        l2, fv = O.lambda2(st, 3.0)
+        d2 = ((st[:, None, :2] - st[None, :, :2]) ** 2).sum(-1)
+        A = np.where((d2 <= 9.0) & ~np.eye(N, dtype=bool), np.exp((9.0 - d2) ** 2 / (81.0 / np.log(2))) - 1, 0.0)
+        w, V = np.linalg.eigh(np.diag(A.sum(1)) - A)
+        assert abs(l2 - w[1]) < 1e-11 * max(1.0, w[-1])
+        assert abs(abs(fv @ V[:, 1]) - 1.0) < 1e-9 and abs(np.linalg.norm(fv) - 1.0) < 1e-12
+
+
+def test_cbf_filter_oracle_kkt(O):
+    # ConnectivityControl::optimize restated: the filtered input satisfies every row it was built
+    # from, equals the desired input when nothing binds, and is the projection otherwise
+    cfg = O.base_config(d_min=0.8, d_max=3.0, num_agents=4, v_min=[-1, -1, -1], v_max=[1, 1, 1])
+    st = np.zeros((2, 4, 6))
+    st[0, :, :2] = [[0, 0], [1.5, 0.2], [0.4, 1.6], [1.9, 1.8]]
+    st[1, :, :2] = [[0, 0], [0.9, 0], [0, 1.0], [5.0, 5.0]]      # agent 3 out of range: lambda2 = 0 -> CLF rows
+    st[:, :, 3:5] = 0.1
+    du = np.zeros((2, 4, 3))
+    du[:, :, 0] = 0.3
+    r = O.cbf_filter_batch(cfg, st, du)
+    assert r["lambda2"][0] > 0.1 and r["lambda2"][1] < 1e-9
+    for s in range(2):
+        for a in range(4):
+            if r["status"][s, a] != 0:
+                continue
+            u = r["u"][s, a]
+            for j in range(4):
+                if j != a:
+                    Ac, Bc = O.safety_cbf_row(st[s, a], st[s, j], 0.8)
+                    assert Ac @ u + Bc >= -1e-8 * max(1.0, abs(Bc))
+            assert np.all(u >= -(st[s, a, 3:] + 1.0) - 1e-9) and np.all(u <= 1.0 - st[s, a, 3:] + 1e-9)
+    assert (r["status"][0] == 0).all()
+
+
 def test_double_integrator_one_step(O):
     # model/tests/DoubleIntegratorXYYawTest.cpp:19-47
     nxt = O.double_integrator_apply(0.1, [1.0, 2.0, 0.5, 0.1, 0.2, 0.3], [0.5, 0.6, 0.1])
