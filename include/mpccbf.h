@@ -166,6 +166,33 @@ int mpccbf_solve_qp_dense(mpccbf_handle* h, int32_t batch, int32_t n, int32_t m,
 int mpccbf_cbf_rows(mpccbf_handle* h, int32_t num_scenarios, const double* states, double* rows,
                     void* cuda_stream);
 
+/* ---- CBF-only safety / connectivity filter ------------------------------
+ * == cbf::ConnectivityControl<double,3>::optimize(cbf_u, desired_u, current_states, self_idx, u_min,
+ * u_max)  cbf/include/cbf/controller/ConnectivityControl.h:16-60, cbf/src/controller/
+ * ConnectivityControl.cpp:22-99 (slack_mode = false) for EVERY agent of every scenario (Jacobi):
+ *      min |u - desired_u|^2   s.t.  pairwise safety HOCBF rows, velocity CBF rows (cfg v_min/v_max),
+ *      the lambda2-connectivity HOCBF row when lambda2 > 0.1, else one distance-CLF row per neighbour
+ * (ConnectivityQPGenerator.cpp:13-150; the u_min/u_max box is commented out in the reference, :60).
+ *   states    [S][N][6]   desired_u [S][N][3]
+ *   u         [S][N][3]   filtered input; zeros where the QP is not OPTIMAL (the reference example
+ *                         falls back to zero control: CBFFormationControl_example.cpp:168-172)
+ *   status    [S][N]      SolveStatus;  lambda2 [S] algebraic connectivity (may be NULL)
+ * One warp per scenario: num_agents <= 32, else MPCCBF_ERR_UNSUPPORTED. Uses cfg d_min, d_max,
+ * cbf_gamma, v_min, v_max, feas_tol. Device pointers, async on `cuda_stream`. */
+int mpccbf_cbf_filter_batch(mpccbf_handle* h, int32_t num_scenarios, const double* states,
+                            const double* desired_u, double* u, int32_t* status, double* lambda2,
+                            void* cuda_stream);
+/* Same with HOST pointers (copies in, runs, copies out, synchronises). */
+int mpccbf_cbf_filter_batch_host(mpccbf_handle* h, int32_t num_scenarios, const double* states,
+                                 const double* desired_u, double* u, int32_t* status, double* lambda2);
+
+/* Sub-kernel: lambda2 and the connectivity HOCBF row of every agent ==
+ * ConnectivityCBF::getLambda2 / initConnCBF / getConnConstraints / getConnBound
+ * (cbf/src/detail/ConnectivityCBF.cpp:388-424,472-552). rows [S][N][4] = (ax, ay, az = 0, b) meaning
+ * a.u + b >= 0; lambda2 [S]. Device pointers, async on stream. num_agents <= 32. */
+int mpccbf_conn_rows(mpccbf_handle* h, int32_t num_scenarios, const double* states, double* rows,
+                     double* lambda2, void* cuda_stream);
+
 /* Sub-kernel K3: advance every agent along its curve by one MPC step, i.e. the state after the
  * h/Ts rollout sub-steps of MPCCBFFormationControl_example.cpp:191-205 without noise:
  * next[S][N][6] = (curve(h), curve'(h)); agents whose n_curves == 0 keep their position with zero

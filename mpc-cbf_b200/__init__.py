@@ -32,6 +32,7 @@ EXPORTED_SYMBOLS = [
     "mpccbf_solve_qp_dense", "mpccbf_cbf_rows", "mpccbf_rollout", "mpccbf_rollout_agents", "mpccbf_step_agents",
     "mpccbf_last_iteration_counts", "mpccbf_copy_iteration_counts", "mpccbf_measure_fp64_tflops", "mpccbf_get_table",
     "mpccbf_linear_cost", "mpccbf_get_counters", "mpccbf_host_alloc", "mpccbf_host_free",
+    "mpccbf_cbf_filter_batch", "mpccbf_cbf_filter_batch_host", "mpccbf_conn_rows",
 ]
 
 
@@ -117,6 +118,9 @@ def lib(path=None):
     L.mpccbf_solve_qp_dense.argtypes = [vp, i32, i32, i32] + [vp] * 11
     L.mpccbf_cbf_rows.argtypes = [vp, i32, vp, vp, vp]
     L.mpccbf_rollout.argtypes = [vp, i32, vp, vp, vp, vp, vp]
+    L.mpccbf_cbf_filter_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+    L.mpccbf_cbf_filter_batch_host.argtypes = [vp, i32, vp, vp, vp, vp, vp]
+    L.mpccbf_conn_rows.argtypes = [vp, i32, vp, vp, vp, vp]
     L.mpccbf_rollout_agents.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp]
     L.mpccbf_last_iteration_counts.argtypes = [vp]
     L.mpccbf_last_iteration_counts.restype = vp
@@ -238,6 +242,15 @@ class Handle:
                                                    _ptr(out["n_curves"]), _ptr(out["objective"])))
         return out
 
+    def cbf_filter_batch_host(self, states, desired_u):
+        """cbf::ConnectivityControl::optimize for every agent: dict(u [S][N][3], status [S][N], lambda2 [S])."""
+        states, desired_u = _f64(states), _f64(desired_u)
+        S, N = states.shape[0], states.shape[1]
+        out = dict(u=np.zeros((S, N, 3)), status=np.zeros((S, N), dtype=np.int32), lambda2=np.zeros(S))
+        self._check(self._L.mpccbf_cbf_filter_batch_host(self._h, S, states.ctypes.data, desired_u.ctypes.data,
+                                                         _ptr(out["u"]), _ptr(out["status"]), _ptr(out["lambda2"])))
+        return out
+
     def optimize_one(self, states, self_idx, ref):
         states, ref = _f64(states), _f64(ref)
         it = self.cfg.impc_iter
@@ -278,6 +291,13 @@ class Handle:
 
     def cbf_rows(self, S, states, rows, stream=None):
         self._check(self._L.mpccbf_cbf_rows(self._h, S, _ptr(states), _ptr(rows), stream))
+
+    def cbf_filter_batch(self, S, states, desired_u, u, status, lambda2=None, stream=None):
+        self._check(self._L.mpccbf_cbf_filter_batch(self._h, S, _ptr(states), _ptr(desired_u), _ptr(u), _ptr(status),
+                                                    _ptr(lambda2), stream))
+
+    def conn_rows(self, S, states, rows, lambda2=None, stream=None):
+        self._check(self._L.mpccbf_conn_rows(self._h, S, _ptr(states), _ptr(rows), _ptr(lambda2), stream))
 
     def rollout(self, S, states, ctrl_pts, n_curves, next_states, stream=None):
         self._check(self._L.mpccbf_rollout(self._h, S, _ptr(states), _ptr(ctrl_pts), _ptr(n_curves),

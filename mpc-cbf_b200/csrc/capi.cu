@@ -573,6 +573,69 @@ int mpccbf_cbf_rows(mpccbf_handle* h, int32_t S, const double* states, double* r
     return MPCCBF_OK;
 }
 
+int mpccbf_cbf_filter_batch(mpccbf_handle* h, int32_t S, const double* states, const double* desired_u, double* u,
+                            int32_t* status, double* lambda2, void* cuda_stream) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (S < 0 || !states || !desired_u || !u || !status) {
+        set_error("mpccbf_cbf_filter_batch: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (h->cfg.num_agents > 32) {
+        set_error("mpccbf_cbf_filter_batch: one lane per agent, num_agents must be <= 32");
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(launch_cbf_filter(h->cfg, S, states, desired_u, u, status, lambda2, nullptr, h->sm_count,
+                               static_cast<cudaStream_t>(cuda_stream)));
+    h->launches += 1;
+    h->qps += static_cast<int64_t>(S) * h->cfg.num_agents;
+    return MPCCBF_OK;
+}
+
+int mpccbf_cbf_filter_batch_host(mpccbf_handle* h, int32_t S, const double* states, const double* desired_u, double* u,
+                                 int32_t* status, double* lambda2) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (S < 0 || S > h->cfg.max_scenarios || !states || !desired_u || !u || !status) {
+        set_error("mpccbf_cbf_filter_batch_host: invalid argument (num_scenarios must be <= max_scenarios)");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (S == 0) return MPCCBF_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    const size_t B = static_cast<size_t>(S) * h->cfg.num_agents;
+    cudaStream_t st = h->stream;
+    // workspaces of the controller path are reused: w_targets [B][3] <- desired_u, w_ctrl (>= [B][3]) <- u,
+    // w_obj [B] (>= [S]) <- lambda2
+    CUDA_TRY(cudaMemcpyAsync(h->w_states, states, sizeof(double) * B * 6, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(h->w_targets, desired_u, sizeof(double) * B * 3, cudaMemcpyHostToDevice, st));
+    rc = mpccbf_cbf_filter_batch(h, S, h->w_states, h->w_targets, h->w_ctrl, h->w_status, h->w_obj, st);
+    if (rc != MPCCBF_OK) return rc;
+    CUDA_TRY(cudaMemcpyAsync(u, h->w_ctrl, sizeof(double) * B * 3, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(status, h->w_status, sizeof(int32_t) * B, cudaMemcpyDeviceToHost, st));
+    if (lambda2) CUDA_TRY(cudaMemcpyAsync(lambda2, h->w_obj, sizeof(double) * S, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return MPCCBF_OK;
+}
+
+int mpccbf_conn_rows(mpccbf_handle* h, int32_t S, const double* states, double* rows, double* lambda2, void* cuda_stream) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (S < 0 || !states || !rows) {
+        set_error("mpccbf_conn_rows: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (h->cfg.num_agents > 32) {
+        set_error("mpccbf_conn_rows: one lane per agent, num_agents must be <= 32");
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(launch_cbf_filter(h->cfg, S, states, nullptr, nullptr, nullptr, lambda2, rows, h->sm_count,
+                               static_cast<cudaStream_t>(cuda_stream)));
+    h->launches += 1;
+    return MPCCBF_OK;
+}
+
 int mpccbf_rollout(mpccbf_handle* h, int32_t S, const double* states, const double* ctrl_pts,
                    const int32_t* n_curves, double* next_states, void* cuda_stream) {
     if (!h) {

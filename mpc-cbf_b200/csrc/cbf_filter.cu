@@ -1,0 +1,313 @@
+// CBF-only safety / connectivity filter — sm_100a. One WARP per scenario, one lane per agent.
+//
+// Replaces cbf::ConnectivityControl::optimize (cbf/src/controller/ConnectivityControl.cpp:22-99,
+// slack_mode = false) for every agent of every scenario:
+//   1. algebraic connectivity: Laplacian of the exp-weighted proximity graph and its second smallest
+//      eigenpair (ConnectivityCBF::getLambda2, cbf/src/detail/ConnectivityCBF.cpp:388-424) by a cyclic
+//      Jacobi iteration on the N x N matrix held in shared memory — the rotation angle is computed
+//      redundantly by every lane, lane k rotates row/column k;
+//   2. per agent the rows of its 3-variable QP  min |u - u_des|^2 :
+//        safety HOCBF rows (closed form of initSafetyCBF :152-198), velocity CBF rows (:251-284),
+//        the connectivity HOCBF row when lambda2 > 0.1 (initConnCBF :472-519 in closed form),
+//        else one distance-CLF row per neighbour (initCLFCBF :200-243);
+//   3. the QP itself: yaw only meets its two velocity rows (a clamp); x/y is a 2-dof projection
+//      solved by the same dual active-set iteration as the IMPC kernel (gi_solver.h), rows
+//      recomputed from shared memory on every scan.
+#include <cuda_runtime.h>
+
+#include <cmath>
+
+#include "../../include/mpccbf.h"
+#include "gi_solver.h"
+#include "kernels.h"
+
+namespace mpccbf {
+
+namespace {
+
+struct FilterRows {
+    const double* st;   // scenario states [N][6] (shared memory)
+    int N, self;
+    double dmin2, gamma, tol;
+    double vlo[2], vhi[2];  // rows  u_d >= vlo[d],  u_d <= vhi[d]   (d = x, y)
+    int use_conn;
+    double gx, gy, bconn;   // connectivity row  g.u + bconn >= 0
+
+    // row id -> np, rhs with the meaning np.u >= rhs
+    __device__ __forceinline__ void row(int id, double (&np)[2], double& rhs) const {
+        const double* e = st + self * 6;
+        if (id < N - 1) {  // safety HOCBF, neighbour id (skipping self)
+            const double* o = st + (id + (id >= self ? 1 : 0)) * 6;
+            const double dx = e[0] - o[0], dy = e[1] - o[1];
+            const double dvx = e[3] - o[3], dvy = e[4] - o[4];
+            const double h = dx * dx + dy * dy - dmin2;
+            const double lfh = 2.0 * (dx * dvx + dy * dvy);
+            const double lf2h = 2.0 * (dvx * dvx + dvy * dvy);
+            const double lfa = 3.0 * gamma * h * h * (2.0 * dx * e[3] + 2.0 * dy * e[4]);
+            const double psi1 = lfh + gamma * h * h * h;
+            np[0] = 2.0 * dx;
+            np[1] = 2.0 * dy;
+            rhs = -(lf2h + lfa + gamma * psi1 * psi1 * psi1);
+        } else if (id < N + 3) {  // velocity CBF rows: x min, y min, x max, y max
+            const int r = id - (N - 1), d = r & 1, up = r >> 1;
+            np[0] = (d == 0) ? (up ? -1.0 : 1.0) : 0.0;
+            np[1] = (d == 1) ? (up ? -1.0 : 1.0) : 0.0;
+            rhs = up ? -(d ? vhi[1] : vhi[0]) : (d ? vlo[1] : vlo[0]);
+        } else if (use_conn) {
+            np[0] = gx;
+            np[1] = gy;
+            rhs = -bconn;
+        } else {  // distance CLF, neighbour id - (N + 3):  Ac.u <= -Bc
+            const int j = id - (N + 3);
+            const double* o = st + (j + (j >= self ? 1 : 0)) * 6;
+            const double dx = e[0] - o[0], dy = e[1] - o[1];
+            const double d2 = dx * dx + dy * dy, dist = sqrt(d2), err = dist - 2.0;
+            const double gxx = 2.0 * err * dx / dist, gyy = 2.0 * err * dy / dist;
+            const double vx = e[3], vy = e[4];
+            const double i1 = 1.0 / dist, i2 = 1.0 / d2, i3 = i1 * i2;
+            const double hxx = 2.0 * (dx * dx * i2 + err * (i1 - dx * dx * i3));
+            const double hxy = 2.0 * (dx * dy * i2 + err * (-dx * dy * i3));
+            const double hyy = 2.0 * (dy * dy * i2 + err * (i1 - dy * dy * i3));
+            const double lfv = gxx * vx + gyy * vy;
+            const double lf2v = vx * (hxx * vx + hxy * vy) + vy * (hxy * vx + hyy * vy);
+            np[0] = -gxx;
+            np[1] = -gyy;
+            rhs = lf2v + 5.0 * lfv + 2.0 * err * err;
+        }
+    }
+    __device__ __forceinline__ int num_rows() const { return (N - 1) + 4 + (use_conn ? 1 : (N - 1)); }
+    __device__ __forceinline__ void scan(const double (&v)[2], double& best, int& best_id) const {
+        const int m = num_rows();
+        for (int id = 0; id < m; ++id) {
+            double np[2], rhs;
+            row(id, np, rhs);
+            const double viol = rhs - fma(np[0], v[0], np[1] * v[1]);
+            if (viol > tol * fmax(1.0, fabs(rhs)) && fabs(rhs) < 1e20) {
+                const double n2 = fma(np[0], np[0], np[1] * np[1]);
+                const double score = (n2 > 0.0) ? viol * rsqrt(n2) : HUGE_VAL;
+                if (score > best) {
+                    best = score;
+                    best_id = id;
+                }
+            }
+        }
+    }
+    __device__ __forceinline__ void normal(int id, double (&np)[2], double& rhs) const { row(id, np, rhs); }
+};
+
+struct FilterArgs {
+    const double* states;     // [S][N][6]
+    const double* desired_u;  // [S][N][3]   (may be NULL when only rows are wanted)
+    double* u;                // [S][N][3]   (may be NULL)
+    int32_t* status;          // [S][N]      (may be NULL)
+    double* lambda2;          // [S]         (may be NULL)
+    double* conn_rows;        // [S][N][4] (gx, gy, 0, b), may be NULL
+    int S, N, NP;             // NP: padded row length (odd)
+    double dmin2, dmax, gamma, tol;
+    double vmin[3], vmax[3];
+    int max_gi;
+};
+
+__global__ void __launch_bounds__(128) cbf_filter_kernel(const FilterArgs a) {
+    extern __shared__ __align__(16) double fsm[];
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int N = a.N, NP = a.NP;
+    const int per_warp = N * 6 + 2 * N * NP + N;
+    double* st = fsm + static_cast<size_t>(wid) * per_warp;
+    double* Lm = st + N * 6;
+    double* Vm = Lm + N * NP;
+    double* fv = Vm + N * NP;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    const double R2 = a.dmax * a.dmax, sigma = R2 * R2 / log(2.0);
+
+    for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < a.S; s += warps) {
+        const double* src = a.states + static_cast<size_t>(s) * N * 6;
+        for (int i = lane; i < N * 6; i += 32) st[i] = __ldg(src + i);
+        __syncwarp();
+        // ---- Laplacian (lane = row), V = I ---------------------------------------------------
+        if (lane < N) {
+            double deg = 0.0;
+            for (int j = 0; j < N; ++j) {
+                double w = 0.0;
+                if (j != lane) {
+                    const double dx = st[lane * 6] - st[j * 6], dy = st[lane * 6 + 1] - st[j * 6 + 1];
+                    const double d2 = dx * dx + dy * dy;
+                    if (d2 <= R2) w = exp((R2 - d2) * (R2 - d2) / sigma) - 1.0;
+                }
+                Lm[lane * NP + j] = -w;
+                Vm[lane * NP + j] = (j == lane) ? 1.0 : 0.0;
+                deg += w;
+            }
+            Lm[lane * NP + lane] = deg;
+        }
+        __syncwarp();
+        // ---- cyclic Jacobi ---------------------------------------------------------------------
+        for (int sweep = 0; sweep < 60 && N > 1; ++sweep) {
+            double off = 0.0, dg = 0.0;
+            if (lane < N)
+                for (int j = 0; j < N; ++j) {
+                    const double x = Lm[lane * NP + j];
+                    if (j == lane) dg = x * x; else off = fma(x, x, off);
+                }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                off += __shfl_xor_sync(full, off, o);
+                dg += __shfl_xor_sync(full, dg, o);
+            }
+            if (!(off > 4.930380657631324e-32 * dg)) break;  // eps^2
+            for (int p = 0; p < N - 1; ++p)
+                for (int q = p + 1; q < N; ++q) {
+                    const double apq = Lm[p * NP + q];
+                    if (apq == 0.0) continue;  // warp-uniform
+                    const double app = Lm[p * NP + p], aqq = Lm[q * NP + q];
+                    const double theta = (aqq - app) / (2.0 * apq);
+                    const double t = copysign(1.0, theta) / (fabs(theta) + sqrt(fma(theta, theta, 1.0)));
+                    const double c = rsqrt(fma(t, t, 1.0)), sn = t * c;
+                    __syncwarp();
+                    if (lane < N) {
+                        const int k = lane;
+                        if (k != p && k != q) {
+                            const double akp = Lm[k * NP + p], akq = Lm[k * NP + q];
+                            const double nkp = c * akp - sn * akq, nkq = sn * akp + c * akq;
+                            Lm[k * NP + p] = nkp;
+                            Lm[p * NP + k] = nkp;
+                            Lm[k * NP + q] = nkq;
+                            Lm[q * NP + k] = nkq;
+                        }
+                        const double vkp = Vm[k * NP + p], vkq = Vm[k * NP + q];
+                        Vm[k * NP + p] = c * vkp - sn * vkq;
+                        Vm[k * NP + q] = sn * vkp + c * vkq;
+                    }
+                    __syncwarp();
+                    if (lane == 0) {
+                        Lm[p * NP + p] = app - t * apq;
+                        Lm[q * NP + q] = aqq + t * apq;
+                        Lm[p * NP + q] = 0.0;
+                        Lm[q * NP + p] = 0.0;
+                    }
+                    __syncwarp();
+                }
+        }
+        // ---- second smallest eigenvalue and its (normalised) eigenvector ---------------------------
+        double lam2 = 0.0;
+        if (N > 1) {
+            const double dv = (lane < N) ? Lm[lane * NP + lane] : HUGE_VAL;
+            double m1 = dv;
+            int i1 = lane;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const double om = __shfl_xor_sync(full, m1, o);
+                const int oi = __shfl_xor_sync(full, i1, o);
+                if (om < m1 || (om == m1 && oi < i1)) { m1 = om; i1 = oi; }
+            }
+            double m2 = (lane == i1) ? HUGE_VAL : dv;
+            int i2 = lane;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const double om = __shfl_xor_sync(full, m2, o);
+                const int oi = __shfl_xor_sync(full, i2, o);
+                if (om < m2 || (om == m2 && oi < i2)) { m2 = om; i2 = oi; }
+            }
+            lam2 = m2;
+            double x = (lane < N) ? Vm[lane * NP + i2] : 0.0;
+            double nn = x * x;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) nn += __shfl_xor_sync(full, nn, o);
+            if (lane < N) fv[lane] = x * rsqrt(nn);
+        } else if (lane < N) {
+            fv[lane] = 0.0;
+        }
+        __syncwarp();
+        if (lane == 0 && a.lambda2) a.lambda2[s] = lam2;
+
+        // ---- per agent: rows and the 3-variable QP --------------------------------------------------
+        if (lane < N) {
+            const int self = lane;
+            const size_t g = static_cast<size_t>(s) * N + self;
+            const double* e = st + self * 6;
+            // connectivity HOCBF row (closed form; eigenvector held constant, no range gating)
+            double gx = 0.0, gy = 0.0, hxx = 0.0, hxy = 0.0, hyy = 0.0;
+            for (int j = 0; j < N; ++j) {
+                if (j == self) continue;
+                const double dx = e[0] - st[j * 6], dy = e[1] - st[j * 6 + 1];
+                const double diff = R2 - (dx * dx + dy * dy);
+                const double E = exp(diff * diff / sigma);
+                const double dvj = fv[self] - fv[j], wj = dvj * dvj;
+                const double c = -4.0 * E * diff / sigma;
+                const double cp2 = 2.0 * (4.0 * E / sigma * (2.0 * diff * diff / sigma + 1.0));
+                gx = fma(c * wj, dx, gx);
+                gy = fma(c * wj, dy, gy);
+                hxx += wj * (c + cp2 * dx * dx);
+                hxy += wj * (cp2 * dx * dy);
+                hyy += wj * (c + cp2 * dy * dy);
+            }
+            const double vx = e[3], vy = e[4];
+            const double lfh = gx * vx + gy * vy;
+            const double lf2h = vx * (hxx * vx + hxy * vy) + vy * (hxy * vx + hyy * vy);
+            const double bconn = lf2h + a.gamma * lfh + a.gamma * (lfh + a.gamma * (lam2 - 0.1));
+            if (a.conn_rows) {
+                double* r = a.conn_rows + g * 4;
+                r[0] = gx; r[1] = gy; r[2] = 0.0; r[3] = bconn;
+            }
+            if (a.u && a.desired_u) {
+                const double* du = a.desired_u + g * 3;
+                FilterRows rows;
+                rows.st = st; rows.N = N; rows.self = self;
+                rows.dmin2 = a.dmin2; rows.gamma = a.gamma; rows.tol = a.tol;
+                rows.vlo[0] = -(e[3] - a.vmin[0]); rows.vhi[0] = a.vmax[0] - e[3];
+                rows.vlo[1] = -(e[4] - a.vmin[1]); rows.vhi[1] = a.vmax[1] - e[4];
+                rows.use_conn = lam2 > 0.1;
+                rows.gx = gx; rows.gy = gy; rows.bconn = bconn;
+                GIState<2> gi;
+                const double v0[2] = {__ldg(du), __ldg(du + 1)};
+                gi_init<2>(gi, v0);
+                int iters = 0;
+                int stat = gi_run<2>(gi, rows, a.max_gi, iters);
+                // yaw: -(w - wmin) <= u <= wmax - w
+                const double ylo = -(e[5] - a.vmin[2]), yhi = a.vmax[2] - e[5];
+                if (ylo > yhi + a.tol * fmax(1.0, fabs(yhi))) stat = (stat == MPCCBF_STATUS_OPTIMAL) ? MPCCBF_STATUS_INFEASIBLE : stat;
+                const double uy = fmin(fmax(__ldg(du + 2), ylo), yhi);
+                const bool ok = stat == MPCCBF_STATUS_OPTIMAL;
+                a.u[g * 3 + 0] = ok ? gi.v[0] : 0.0;
+                a.u[g * 3 + 1] = ok ? gi.v[1] : 0.0;
+                a.u[g * 3 + 2] = ok ? uy : 0.0;
+                if (a.status) a.status[g] = stat;
+            }
+        }
+        __syncwarp();
+    }
+}
+
+}  // namespace
+
+// Returns a cudaError_t; cudaErrorInvalidValue when N > 32 (one lane per agent).
+int launch_cbf_filter(const mpccbf_config& cfg, int S, const double* states, const double* desired_u, double* u,
+                      int32_t* status, double* lambda2, double* conn_rows, int sm_count, cudaStream_t stream) {
+    if (S <= 0) return cudaSuccess;
+    const int N = cfg.num_agents;
+    if (N > 32 || N < 1) return cudaErrorInvalidValue;
+    FilterArgs a;
+    a.states = states; a.desired_u = desired_u; a.u = u; a.status = status; a.lambda2 = lambda2; a.conn_rows = conn_rows;
+    a.S = S; a.N = N; a.NP = N | 1;
+    a.dmin2 = cfg.d_min * cfg.d_min; a.dmax = cfg.d_max;
+    a.gamma = cfg.cbf_gamma > 0 ? cfg.cbf_gamma : 5.0;
+    a.tol = cfg.feas_tol > 0 ? cfg.feas_tol : 1e-9;
+    for (int d = 0; d < 3; ++d) { a.vmin[d] = cfg.v_min[d]; a.vmax[d] = cfg.v_max[d]; }
+    a.max_gi = 50 * (2 * N + 4) + 100;
+    const int threads = 128;
+    const size_t per_warp = sizeof(double) * (N * 6 + 2 * N * a.NP + N);
+    const size_t smem = per_warp * (threads / 32);
+    cudaError_t e = cudaFuncSetAttribute(cbf_filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    int per_sm = 1;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cbf_filter_kernel, threads, smem);
+    if (e != cudaSuccess) return e;
+    const int need = (S + threads / 32 - 1) / (threads / 32);
+    int grid = sm_count * (per_sm < 1 ? 1 : per_sm);  // persistent: a multiple of the SM count
+    if (need < grid) grid = need;
+    cbf_filter_kernel<<<grid, threads, smem, stream>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace mpccbf

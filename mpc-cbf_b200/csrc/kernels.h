@@ -5,6 +5,7 @@
 
 #include <string>
 
+#include "../../include/mpccbf.h"
 #include "device_tables.h"
 
 struct mpccbf_handle;
@@ -38,6 +39,8 @@ int launch_cbf_rows(const double* states, double* rows, int S, int N, double dmi
                     int sm_count, cudaStream_t stream);
 int launch_rollout(const double* states, const double* ctrl, const int32_t* n_curves, double* next,
                    int B, const RolloutConst& rc, cudaStream_t stream);
+int launch_cbf_filter(const mpccbf_config& cfg, int S, const double* states, const double* desired_u, double* u,
+                      int32_t* status, double* lambda2, double* conn_rows, int sm_count, cudaStream_t stream);
 struct DenseOpts {
     int max_iter, check_every;  // <= 0: defaults (20000, 10)
     double eps, rho, sigma;     // <= 0: defaults (1e-7, 0.1, 1e-6)
