@@ -193,6 +193,32 @@ int mpccbf_cbf_filter_batch_host(mpccbf_handle* h, int32_t num_scenarios, const 
 int mpccbf_conn_rows(mpccbf_handle* h, int32_t num_scenarios, const double* states, double* rows,
                      double* lambda2, void* cuda_stream);
 
+/* ---- Device-resident closed-loop episodes ----------------------------------------
+ * Runs `num_control_steps` control steps of every scenario without leaving the device: batched
+ * optimize (== mpccbf_step_batch), then each agent follows its newest successful curve for h / Ts
+ * sub-steps exactly like the reference's experiment driver (noise-free, Jacobi order)
+ *      mpc_cbf/examples/connectivity/MPCCBFFormationControl_example.cpp:135-231
+ * (an agent whose optimize fails keeps following its previous curve, the parameter clamped to
+ * max_parameter; one that never had a curve stays put with zero velocity), and the success metric of
+ *      workspace/experiments/python/metrics/collision_check.py:48-79  (instance_success, circle shape)
+ * is updated at every sub-step.
+ *   states       [S][N][6]  in: start states, out: final states            device pointer
+ *   targets      [S][N][3]  goals (tasks.sf)                               device pointer
+ *   goal_radius             reach_goal_area radius (1.0 in the reference)
+ *   collision_radius        robot_params.collision_shape.radius: overlap when dist <= 2 r
+ *   success      [S]  1 unless two agents overlapped before every agent had reached its goal area
+ *   finish_step  [S]  the sub-step index instance_success returns (number of sub-steps when the goals
+ *                     were not all reached; -1 for its float('inf'))
+ *   min_dist     [S]  smallest pairwise centre distance over all sub-steps
+ *   failed_calls [S]  optimize calls that returned fewer than impc_iter curves
+ *   traj         NULL or [S][N][num_control_steps * (h/Ts)][6]: every sub-step state (states.json)
+ * Output pointers may be NULL individually. Device pointers; the call is asynchronous on
+ * `cuda_stream` except for its first use on a handle (workspace allocation). */
+int mpccbf_run_episode(mpccbf_handle* h, int32_t num_scenarios, double* states, const double* targets,
+                       int32_t num_control_steps, double goal_radius, double collision_radius,
+                       int32_t* success, int32_t* finish_step, double* min_dist, int32_t* failed_calls,
+                       double* traj, void* cuda_stream);
+
 /* Sub-kernel K3: advance every agent along its curve by one MPC step, i.e. the state after the
  * h/Ts rollout sub-steps of MPCCBFFormationControl_example.cpp:191-205 without noise:
  * next[S][N][6] = (curve(h), curve'(h)); agents whose n_curves == 0 keep their position with zero

@@ -32,7 +32,7 @@ EXPORTED_SYMBOLS = [
     "mpccbf_solve_qp_dense", "mpccbf_cbf_rows", "mpccbf_rollout", "mpccbf_rollout_agents", "mpccbf_step_agents",
     "mpccbf_last_iteration_counts", "mpccbf_copy_iteration_counts", "mpccbf_measure_fp64_tflops", "mpccbf_get_table",
     "mpccbf_linear_cost", "mpccbf_get_counters", "mpccbf_host_alloc", "mpccbf_host_free",
-    "mpccbf_cbf_filter_batch", "mpccbf_cbf_filter_batch_host", "mpccbf_conn_rows",
+    "mpccbf_cbf_filter_batch", "mpccbf_cbf_filter_batch_host", "mpccbf_conn_rows", "mpccbf_run_episode",
 ]
 
 
@@ -121,6 +121,7 @@ def lib(path=None):
     L.mpccbf_cbf_filter_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
     L.mpccbf_cbf_filter_batch_host.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     L.mpccbf_conn_rows.argtypes = [vp, i32, vp, vp, vp, vp]
+    L.mpccbf_run_episode.argtypes = [vp, i32, vp, vp, i32, dbl, dbl, vp, vp, vp, vp, vp, vp]
     L.mpccbf_rollout_agents.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp]
     L.mpccbf_last_iteration_counts.argtypes = [vp]
     L.mpccbf_last_iteration_counts.restype = vp
@@ -295,6 +296,13 @@ class Handle:
     def cbf_filter_batch(self, S, states, desired_u, u, status, lambda2=None, stream=None):
         self._check(self._L.mpccbf_cbf_filter_batch(self._h, S, _ptr(states), _ptr(desired_u), _ptr(u), _ptr(status),
                                                     _ptr(lambda2), stream))
+
+    def run_episode(self, S, states, targets, steps, goal_radius, collision_radius, success=None, finish_step=None,
+                    min_dist=None, failed_calls=None, traj=None, stream=None):
+        """Closed-loop episode on the device (states is updated in place); see include/mpccbf.h."""
+        self._check(self._L.mpccbf_run_episode(self._h, S, _ptr(states), _ptr(targets), steps, goal_radius,
+                                               collision_radius, _ptr(success), _ptr(finish_step), _ptr(min_dist),
+                                               _ptr(failed_calls), _ptr(traj), stream))
 
     def conn_rows(self, S, states, rows, lambda2=None, stream=None):
         self._check(self._L.mpccbf_conn_rows(self._h, S, _ptr(states), _ptr(rows), _ptr(lambda2), stream))

@@ -41,6 +41,10 @@ struct mpccbf_handle {
     // single-agent workspace (optimize_one)
     double *o_states = nullptr, *o_ref = nullptr, *o_ctrl = nullptr, *o_all = nullptr;
     int32_t* o_status = nullptr;
+    // episode driver workspaces (allocated on first use)
+    double *e_curve = nullptr, *e_evalt = nullptr, *e_mind2 = nullptr, *e_ctrl = nullptr;
+    int32_t *e_has = nullptr, *e_done = nullptr, *e_finish = nullptr, *e_failed = nullptr, *e_status = nullptr, *e_nc = nullptr;
+    unsigned char* e_reached = nullptr;
     int64_t launches = 0, qps = 0;
 };
 
@@ -379,6 +383,10 @@ int mpccbf_destroy(mpccbf_handle* h) {
     if (!h) return MPCCBF_OK;
     if (h->has_device) {
         cudaSetDevice(h->device);
+        void* eptrs[] = {h->e_curve, h->e_ctrl, h->e_evalt, h->e_has, h->e_nc, h->e_status, h->e_reached, h->e_mind2,
+                         h->e_done, h->e_finish, h->e_failed};
+        for (void* q : eptrs)
+            if (q) cudaFree(q);
         void* ptrs[] = {h->d_tmpl, h->d_yw, h->d_vr, h->d_kr, h->w_states, h->w_targets, h->w_ctrl, h->w_obj,
                         h->w_status, h->w_ncurves, h->w_iters, h->o_states, h->o_ref, h->o_ctrl, h->o_all, h->o_status};
         for (void* p : ptrs)
@@ -633,6 +641,70 @@ int mpccbf_conn_rows(mpccbf_handle* h, int32_t S, const double* states, double* 
     CUDA_TRY(launch_cbf_filter(h->cfg, S, states, nullptr, nullptr, nullptr, lambda2, rows, h->sm_count,
                                static_cast<cudaStream_t>(cuda_stream)));
     h->launches += 1;
+    return MPCCBF_OK;
+}
+
+int mpccbf_run_episode(mpccbf_handle* h, int32_t S, double* states, const double* targets, int32_t steps, double goal_radius,
+                       double collision_radius, int32_t* success, int32_t* finish_step, double* min_dist, int32_t* failed_calls,
+                       double* traj, void* cuda_stream) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (S < 0 || S > h->cfg.max_scenarios || steps < 0 || !states || !targets) {
+        set_error("mpccbf_run_episode: invalid argument (num_scenarios must be <= max_scenarios)");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (h->tab.c > 8 || h->tab.p > 16) {
+        set_error("mpccbf_run_episode: curves with more than 8 control points or 16 pieces are not supported");
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    if (S == 0) return MPCCBF_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    const size_t B = static_cast<size_t>(h->cfg.max_scenarios) * h->cfg.num_agents, n = h->tab.n, it = h->cfg.impc_iter;
+    if (!h->e_curve) {
+        bool ok = true;
+        ok &= cudaMalloc(&h->e_curve, sizeof(double) * B * n) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_ctrl, sizeof(double) * B * n) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_evalt, sizeof(double) * B) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_has, sizeof(int32_t) * B) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_nc, sizeof(int32_t) * B) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_status, sizeof(int32_t) * B * it) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_reached, B) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_mind2, sizeof(double) * h->cfg.max_scenarios) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_done, sizeof(int32_t) * h->cfg.max_scenarios) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_finish, sizeof(int32_t) * h->cfg.max_scenarios) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_failed, sizeof(int32_t) * h->cfg.max_scenarios) == cudaSuccess;
+        if (!ok) {
+            set_error("mpccbf_run_episode: out of device memory");
+            return MPCCBF_ERR_ALLOC;
+        }
+    }
+    const int N = h->cfg.num_agents;
+    CUDA_TRY(launch_episode_init(S, N, h->e_evalt, h->e_has, h->e_reached, h->e_done, h->e_finish, h->e_mind2, h->e_failed, st));
+    EpisodeArgs a;
+    a.states = states; a.targets = targets; a.ctrl_new = h->e_ctrl; a.n_curves = h->e_nc;
+    a.curve = h->e_curve; a.eval_t = h->e_evalt; a.has_curve = h->e_has; a.reached = h->e_reached;
+    a.done = h->e_done; a.finish = h->e_finish; a.min_dist2 = h->e_mind2; a.failed = h->e_failed; a.traj = traj;
+    a.S = S; a.N = N; a.n = h->tab.n; a.c = h->tab.c; a.p = h->tab.p; a.iters = h->cfg.impc_iter;
+    a.nsub = static_cast<int>(h->cfg.h / h->cfg.Ts);  // int(h / Ts), MPCCBFFormationControl_example.cpp:193
+    a.traj_len = steps * a.nsub;
+    a.Ts = h->cfg.Ts; a.piece_T = h->cfg.piece_max_param;
+    a.goal_radius = goal_radius; a.collision_radius = collision_radius;
+    double cum = 0.0;
+    for (int i = 0; i < 16; ++i) {
+        if (i < h->tab.p) cum += h->cfg.piece_max_param;  // cumulative ends by repeated addition, like the reference
+        a.cum[i] = cum;
+    }
+    a.max_param = cum;
+    for (int step = 0; step < steps; ++step) {
+        rc = run_step(h, S, 0, N, states, targets, 0, h->e_ctrl, nullptr, h->e_status, h->e_nc, nullptr, h->w_iters, st);
+        if (rc != MPCCBF_OK) return rc;
+        a.step = step;
+        CUDA_TRY(launch_episode_advance(a, h->sm_count, st));
+        h->launches += 1;
+    }
+    CUDA_TRY(launch_episode_final(S, steps * a.nsub, h->e_done, h->e_finish, h->e_mind2, success, finish_step, min_dist, st));
+    if (failed_calls) CUDA_TRY(cudaMemcpyAsync(failed_calls, h->e_failed, sizeof(int32_t) * S, cudaMemcpyDeviceToDevice, st));
     return MPCCBF_OK;
 }
 

@@ -41,6 +41,30 @@ int launch_rollout(const double* states, const double* ctrl, const int32_t* n_cu
                    int B, const RolloutConst& rc, cudaStream_t stream);
 int launch_cbf_filter(const mpccbf_config& cfg, int S, const double* states, const double* desired_u, double* u,
                       int32_t* status, double* lambda2, double* conn_rows, int sm_count, cudaStream_t stream);
+// Episode driver (episode.cu): one control step's worth of curve following + metric update.
+struct EpisodeArgs {
+    double* states;            // [S][N][6] in: state the step was solved at; out: state after h
+    const double* targets;     // [S][N][3]
+    const double* ctrl_new;    // [S][N][n] result of this step's optimize
+    const int32_t* n_curves;   // [S][N]
+    double* curve;             // [S][N][n] curve being followed (persistent)
+    double* eval_t;            // [S][N]    its evaluation time (persistent)
+    int32_t* has_curve;        // [S][N]
+    unsigned char* reached;    // [S][N] goal-area flags
+    int32_t* done;             // [S] 0 running, 1 success decided, 2 collision
+    int32_t* finish;           // [S]
+    double* min_dist2;         // [S]
+    int32_t* failed;           // [S] optimize calls that did not return all IMPC iterates (may be NULL)
+    double* traj;              // [S][N][traj_len][6] or NULL
+    int S, N, n, c, p, iters, nsub, step, traj_len;
+    double Ts, piece_T, max_param, goal_radius, collision_radius;
+    double cum[16];            // cumulative piece ends
+};
+int launch_episode_init(int S, int N, double* eval_t, int32_t* has_curve, unsigned char* reached, int32_t* done, int32_t* finish,
+                        double* min_dist2, int32_t* failed, cudaStream_t stream);
+int launch_episode_advance(const EpisodeArgs& a, int sm_count, cudaStream_t stream);
+int launch_episode_final(int S, int total_substeps, const int32_t* done, const int32_t* finish, const double* min_dist2,
+                         int32_t* success, int32_t* finish_step, double* min_dist, cudaStream_t stream);
 struct DenseOpts {
     int max_iter, check_every;  // <= 0: defaults (20000, 10)
     double eps, rho, sigma;     // <= 0: defaults (1e-7, 0.1, 1e-6)

@@ -9,6 +9,7 @@
 #include <iostream>
 #include <limits>
 
+#include "mpccbf_host/cbf_control.hpp"
 #include "mpccbf_host/controller.hpp"
 #include "mpccbf_host/qpcpp.hpp"
 
@@ -215,6 +216,52 @@ static void test_two_robot_swap_on_device() {
     EXPECT_NEAR(r.objective[0], -1378.9905, 1e-3);
 }
 
+// cbf::ConnectivityControl mirror: the reference's TestInitConnectivity geometry (three robots on a
+// line, 2 m apart, dmax 3) is connected (lambda2 = 0.2385 > 0.1), so the connectivity row is used.
+static void test_cbf_filter_on_device() {
+    using Control = cbf::ConnectivityControl<double, DIM>;
+    auto cb = std::make_shared<cbf::ConnectivityCBF>(0.8, 3.0, math::Vector<double>{-3.0, -3.0, -3.0},
+                                                     math::Vector<double>{3.0, 3.0, 3.0});
+    Control ctl(cb, 3);
+    std::vector<State> states(3);
+    states[0].pos_ = {1.0, 2.0, 0.0};
+    states[1].pos_ = {1.0, 4.0, 0.0};
+    states[2].pos_ = {1.0, 6.0, 0.0};
+    math::VectorDIM<double, DIM> u, lim{5.0, 5.0, 5.0}, nlim{-5.0, -5.0, -5.0};
+    // nothing binds: the filter returns the desired input
+    EXPECT(ctl.optimize(u, {0.1, 0.2, 0.05}, states, 1, nlim, lim));
+    EXPECT_NEAR(ctl.last_lambda2(), 0.2385412985210327, 1e-12);
+    EXPECT_NEAR(u(0), 0.1, 1e-12);
+    EXPECT_NEAR(u(1), 0.2, 1e-12);
+    EXPECT_NEAR(u(2), 0.05, 1e-12);
+    // velocity CBF rows: v_x = 2.9, v_max = 3 -> u_x <= 0.1; yaw rate -3.2 < v_min -> u_yaw >= 0.2
+    states[1].vel_ = {2.9, 0.0, -3.2};
+    EXPECT(ctl.optimize(u, {2.0, 0.0, 0.0}, states, 1, nlim, lim));
+    EXPECT_NEAR(u(0), 0.1, 1e-9);
+    EXPECT_NEAR(u(2), 0.2, 1e-9);
+    states[1].vel_ = {0.0, 0.0, 0.0};
+    // the reference's golden row of agent 0 (TestInitConnectivity.cpp:103-127): g = (0, -2.703392),
+    // b = 3.4635..., i.e.  -2.703392 u_y + 3.4635 >= 0  caps u_y at b / |g_y| = 1.2812
+    EXPECT(ctl.optimize(u, {0.0, 4.0, 0.0}, states, 0, nlim, lim));
+    EXPECT_NEAR(u(1), 3.4635324630258153 / 2.70339242, 1e-6);
+    EXPECT_NEAR(u(0), 0.0, 1e-12);
+    EXPECT_THROW(ctl.optimize(u, {0.0, 0.0, 0.0}, states, 3, nlim, lim), std::out_of_range);
+    EXPECT_THROW(Control(cb, 3, true, 1.0, 0.1), std::runtime_error);
+    // batched sibling gives the same answer for the same snapshot
+    cbf::BatchedConnectivityControl<double, DIM> batch(*cb, 3, 2);
+    std::vector<double> st(2 * 3 * 6, 0.0), du(2 * 3 * 3, 0.0);
+    for (int s = 0; s < 2; ++s)
+        for (int i = 0; i < 3; ++i) {
+            st[(s * 3 + i) * 6 + 0] = 1.0;
+            st[(s * 3 + i) * 6 + 1] = 2.0 + 2.0 * i;
+        }
+    du[(1 * 3 + 0) * 3 + 1] = 4.0;
+    auto r = batch.optimize(2, st, du);
+    EXPECT(r.status[3] == MPCCBF_STATUS_OPTIMAL);
+    EXPECT_NEAR(r.u[(1 * 3 + 0) * 3 + 1], u(1), 1e-12);
+    EXPECT_NEAR(r.lambda2[0], r.lambda2[1], 1e-15);
+}
+
 int main(int argc, char** argv) {
     const bool cpu_only = argc > 1 && std::strcmp(argv[1], "--cpu") == 0;
     test_problem_container();
@@ -223,6 +270,7 @@ int main(int argc, char** argv) {
     if (!cpu_only) {
         test_toy_qp_on_device();
         test_two_robot_swap_on_device();
+        test_cbf_filter_on_device();
     }
     std::printf("%s: %d failure(s)%s\n", argv[0], g_fail, cpu_only ? " (cpu-only subset)" : "");
     return g_fail == 0 ? 0 : 1;

@@ -1,0 +1,124 @@
+"""GPU: the device-resident episode driver (mpccbf_run_episode) against (i) the host-driven loop over
+the same C-ABI calls, (ii) the CPU oracle stepped in closed loop, (iii) a numpy restatement of the
+reference's instance_success metric (experiments/python/metrics/collision_check.py:48-79)."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, swarm
+
+pytestmark = pytest.mark.gpu
+
+
+def instance_success(traj, goals, radius, coll_radius):
+    """collision_check.py:48-79, circle shape. traj [N][T][6]. Returns (success, finish) with
+    finish = -1 for float('inf')."""
+    N, T = traj.shape[:2]
+    reach = [False] * N
+    for t in range(T):
+        if all(reach):
+            return True, max(0, t - 1)
+        for i in range(N):
+            if np.linalg.norm(traj[i, t, :2] - goals[i][:2]) <= radius:
+                reach[i] = True
+            for j in range(i + 1, N):
+                if np.hypot(*(traj[j, t, :2] - traj[i, t, :2])) <= 2 * coll_radius:
+                    return False, -1
+    return True, T
+
+
+def run(M, cfg, st, tg, steps, goal_r, coll_r):
+    import torch
+    S, N = st.shape[:2]
+    h = M.Handle(cfg)
+    nsub = int(cfg.h / cfg.Ts)
+    d_st, d_tg = torch.tensor(st, device="cuda"), torch.tensor(tg, device="cuda")
+    out = dict(success=torch.zeros(S, dtype=torch.int32, device="cuda"), finish=torch.zeros(S, dtype=torch.int32, device="cuda"),
+               min_dist=torch.zeros(S, dtype=torch.float64, device="cuda"), failed=torch.zeros(S, dtype=torch.int32, device="cuda"),
+               traj=torch.zeros((S, N, steps * nsub, 6), dtype=torch.float64, device="cuda"))
+    h.run_episode(S, d_st, d_tg, steps, goal_r, coll_r, out["success"], out["finish"], out["min_dist"], out["failed"], out["traj"])
+    torch.cuda.synchronize()
+    res = {k: v.cpu().numpy() for k, v in out.items()}
+    res["final"] = d_st.cpu().numpy()
+    return h, res
+
+
+def test_episode_matches_oracle_closed_loop(M, O):
+    # 2 scenarios x 4 agents, 12 control steps: every sub-step state against the oracle stepped in
+    # closed loop with the reference driver's rules (MPCCBFFormationControl_example.cpp:140-231)
+    S, N, steps = 2, 4, 12
+    cfg = M.default_config(k_hor=16, num_pieces=3, d_min=0.8, num_agents=N, max_scenarios=S)
+    st, tg = swarm(S, N, seed=5)
+    st[:, :, :2] *= 0.5
+    tg[:, :, :2] *= 0.5
+    h, res = run(M, cfg, st, tg, steps, 1.0, 0.2)
+    oc = O.base_config(k_hor=16, num_pieces=3, d_min=0.8, num_agents=N)
+    s = st.copy()
+    prev = [[None] * N for _ in range(S)]
+    et = np.zeros((S, N))
+    maxp = 3 * 0.5
+    for step in range(steps):
+        r = O.step_batch(oc, s, tg, threads=2, prec=1)
+        for sc in range(S):
+            for a in range(N):
+                if r["n_curves"][sc, a] > 0:
+                    prev[sc][a], et[sc, a] = r["ctrl_pts"][sc, a].copy(), 0.0
+        for ti in range(1, 11):
+            for sc in range(S):
+                for a in range(N):
+                    if prev[sc][a] is None:
+                        s[sc, a, 3:] = 0.0
+                        continue
+                    t = min(et[sc, a] + 0.01 * ti, maxp)
+                    s[sc, a, :3] = O.eval_curve(oc, prev[sc][a], t, 0)
+                    s[sc, a, 3:] = O.eval_curve(oc, prev[sc][a], t, 1)
+            assert np.abs(res["traj"][:, :, 10 * step + ti - 1, :] - s).max() < 1e-6, (step, ti)
+        et = np.minimum(et + 0.1, maxp)
+    assert np.abs(res["final"] - s).max() < 1e-6
+    h.close()
+
+
+def test_episode_metrics_and_host_loop(M):
+    import torch
+    # 48 ring-swap scenarios of 8 agents, 70 control steps: metric against the numpy restatement on the
+    # dumped trajectory, final states against the host-driven loop over step_batch + curve following
+    S, N, steps = 48, 8, 70
+    cfg = M.default_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N, max_scenarios=S)
+    st, tg = swarm(S, N, seed=11)
+    st[:, :, :2] *= 0.6
+    tg[:, :, :2] *= 0.6
+    tg[::2, :, :2] = st[::2, :, :2] + [2.5, 1.0]     # every other scenario: a formation translation (no conflicts)
+    coll_r = 0.36
+    h, res = run(M, cfg, st, tg, steps, 1.0, coll_r)
+    nfin, nfail = 0, 0
+    for s in range(S):
+        ok, fin = instance_success(res["traj"][s], tg[s], 1.0, coll_r)
+        assert bool(res["success"][s]) == ok and res["finish"][s] == fin, (s, ok, fin, res["success"][s], res["finish"][s])
+        d = np.linalg.norm(res["traj"][s][:, None, :, :2] - res["traj"][s][None, :, :, :2], axis=-1)
+        d[np.arange(N), np.arange(N)] = np.inf
+        assert abs(d.min() - res["min_dist"][s]) < 1e-12
+        nfin += int(ok and fin < steps * 10)
+        nfail += int(not ok)
+    assert nfin >= S // 2      # the translations complete inside the episode
+    assert np.array_equal(res["final"], res["traj"][:, :, -1, :])
+    # same episode without the trajectory dump and metrics pointers: identical final states
+    d_st = torch.tensor(st, device="cuda")
+    h.run_episode(S, d_st, torch.tensor(tg, device="cuda"), steps, 1.0, coll_r)
+    torch.cuda.synchronize()
+    assert np.array_equal(d_st.cpu().numpy(), res["final"])
+    h.close()
+
+
+def test_episode_two_robot_config(M):
+    # BASELINE configs[0]: the shipped 2-robot swap (circle2_config.json), 200 control steps
+    cfg, so, sf = M.config_from_json(os.path.join(GOLDEN, "circle2_config.json"), max_scenarios=1)
+    assert cfg.num_agents == 2
+    st = np.zeros((1, 2, 6))
+    st[0, :, :3] = so[:2]
+    tg = sf[None, :2, :].copy()
+    h, res = run(M, cfg, st, tg, 200, 1.0, 0.3)
+    assert np.abs(res["final"][0, :, :2] - tg[0, :, :2]).max() < 0.05
+    assert res["traj"].shape == (1, 2, 2000, 6)
+    assert res["failed"][0] > 0          # the exact head-on swap has infeasible steps
+    h.close()
