@@ -28,8 +28,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 METRIC = "mpc_cbf_qps_per_sec"
 # dram__bytes_read.sum + dram__bytes_write.sum of one impc_thread_kernel launch of this workload
-# (ncu --set full, profiles/r1b_impc_thread_ncu_summary.md); None until captured for a new shape
-TRAFFIC_BYTES_PER_LAUNCH = 14.0e6
+# (ncu --set full, profiles/r1g_impc_thread_ncu_summary.md: 11.3 MB read + 67.9 MB written; the part
+# above the 31.7 MB algorithmic bytes is local memory — the stage-A snapshot and register spills —
+# written back from L1/L2); None for other shapes
+TRAFFIC_BYTES_PER_LAUNCH = 79.1e6
 UNIT = "QPs/s"
 
 
