@@ -475,13 +475,22 @@ int mpccbf_step_batch_host(mpccbf_handle* h, int32_t S, const double* states, co
     // instead of writing HBM and copying afterwards. The small per-agent outputs (status, n_curves,
     // objective) are single 4/8-byte stores and stay on the copy path. MPCCBF_ZEROCOPY=0 disables it.
     double* ctrl_dev = nullptr;
+    const double *states_dev = nullptr, *targets_dev = nullptr;  // pinned inputs are read in place as well
     {
         static const bool allow = [] { const char* e = std::getenv("MPCCBF_ZEROCOPY"); return !e || std::atoi(e) != 0; }();
-        cudaPointerAttributes pa;
-        if (allow && cudaPointerGetAttributes(&pa, ctrl_pts) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer)
-            ctrl_dev = static_cast<double*>(pa.devicePointer);
-        else
+        static const bool allow_in = [] { const char* e = std::getenv("MPCCBF_ZEROCOPY_IN"); return !e || std::atoi(e) != 0; }();
+        auto mapped = [](const void* p) -> void* {
+            cudaPointerAttributes pa;
+            if (cudaPointerGetAttributes(&pa, p) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer) return pa.devicePointer;
             (void)cudaGetLastError();
+            return nullptr;
+        };
+        if (allow) ctrl_dev = static_cast<double*>(mapped(ctrl_pts));
+        if (allow && allow_in) {
+            states_dev = static_cast<const double*>(mapped(states));
+            targets_dev = static_cast<const double*>(mapped(targets));
+            if (!states_dev || !targets_dev) states_dev = targets_dev = nullptr;
+        }
     }
     // The batch can also be cut into scenario chunks that alternate between two streams so that
     // copies and kernels overlap (MPCCBF_HOST_CHUNKS). Measured on B200 (profiles/r1d_host_chunks.md)
@@ -496,10 +505,13 @@ int mpccbf_step_batch_host(mpccbf_handle* h, int32_t S, const double* states, co
         const size_t a0 = s0 * N, cnt = (s1 - s0) * N;
         if (cnt == 0) continue;
         cudaStream_t st = streams[c & 1];
-        CUDA_TRY(cudaMemcpyAsync(h->w_states + a0 * 6, states + a0 * 6, sizeof(double) * cnt * 6, cudaMemcpyHostToDevice, st));
-        CUDA_TRY(cudaMemcpyAsync(h->w_targets + a0 * 3, targets + a0 * 3, sizeof(double) * cnt * 3, cudaMemcpyHostToDevice, st));
+        if (!states_dev) {
+            CUDA_TRY(cudaMemcpyAsync(h->w_states + a0 * 6, states + a0 * 6, sizeof(double) * cnt * 6, cudaMemcpyHostToDevice, st));
+            CUDA_TRY(cudaMemcpyAsync(h->w_targets + a0 * 3, targets + a0 * 3, sizeof(double) * cnt * 3, cudaMemcpyHostToDevice, st));
+        }
         double* ctrl_out = ctrl_dev ? ctrl_dev + a0 * n : h->w_ctrl + a0 * n;
-        rc = run_step(h, s1 - s0, 0, h->cfg.num_agents, h->w_states + a0 * 6, h->w_targets + a0 * 3, 0, ctrl_out,
+        rc = run_step(h, s1 - s0, 0, h->cfg.num_agents, states_dev ? states_dev + a0 * 6 : h->w_states + a0 * 6,
+                      states_dev ? targets_dev + a0 * 3 : h->w_targets + a0 * 3, 0, ctrl_out,
                       nullptr, h->w_status + a0 * it, h->w_ncurves + a0, h->w_obj + a0, h->w_iters + a0 * it, st);
         if (rc != MPCCBF_OK) return rc;
         if (!ctrl_dev)

@@ -100,6 +100,12 @@ def test_device_pointer_step_rollout_and_agent_shards(M, O, torch):
     h.step_batch_host(st, tg, out={k: v.numpy() for k, v in pinned.items()})
     for k in pinned:
         assert np.array_equal(pinned[k].numpy(), host[k]), k
+    # ... and pinned inputs are read by the kernel in place
+    pst, ptg = torch.tensor(st).pin_memory(), torch.tensor(tg).pin_memory()
+    pinned["ctrl_pts"].fill_(float("nan"))
+    h.step_batch_host(pst.numpy(), ptg.numpy(), out={k: v.numpy() for k, v in pinned.items()})
+    for k in pinned:
+        assert np.array_equal(pinned[k].numpy(), host[k]), k
     # agent-sharded launch: two halves reproduce the whole
     for begin, cnt in ((0, 8), (8, 8), (5, 3)):
         cp2 = torch.zeros((S, cnt, h.n), dtype=torch.float64, device="cuda")
