@@ -194,6 +194,63 @@ __device__ bool factorize(const Ctx& c, const double* wv, double shift) {
     return ok;
 }
 
+// Explicit inverse for the ADMM loop. The triangular solves of chol_solve are a serial chain of 2n
+// steps run by one warp while the other seven wait (42 % of the kernel's stall samples in
+// profiles/r1g_subkernels_ncu_summary.md); the loop applies the SAME matrix hundreds of times between
+// refactorisations, so it pays to form Minv = (L L')^-1 once (W = L^-1 in place, then Minv = W'W by
+// all threads) and turn every solve into a dense n x n mat-vec. Minv overwrites c.L:
+// callers that need the factor again (polish) refactorise first, which they already do.
+__device__ void invert_factor(const Ctx& c) {
+    const int n = c.n, t = threadIdx.x;
+    // W = L^-1 in place, last column first: W[j+1:, j] = -W[j+1:, j+1:] L[j+1:, j] / L_jj  (dtrti2)
+    for (int j = n - 1; j >= 0; --j) {
+        double s = 0.0;
+        if (t > j && t < n) {
+            const double* wi = c.L + t * c.ldl;
+            for (int k = j + 1; k <= t; ++k) s = fma(wi[k], c.L[k * c.ldl + j], s);
+        }
+        __syncthreads();  // column j of L has been read by everyone
+        if (t > j && t < n) c.L[t * c.ldl + j] = -s * c.invd[j];
+        if (t == j) c.L[j * c.ldl + j] = c.invd[j];
+        __syncthreads();
+    }
+    // Minv = W'W: strictly-lower entries go to the (free) upper triangle, the diagonal to invd, then
+    // the upper triangle is mirrored down once nobody reads W any more
+    for (int e = t; e < n * n; e += kT) {
+        const int a = e / n, b = e - a * n;
+        if (b > a) continue;
+        double s = 0.0;
+        for (int k = a; k < n; ++k) s = fma(c.L[k * c.ldl + a], c.L[k * c.ldl + b], s);
+        if (a == b) c.part[a] = s; else c.L[b * c.ldl + a] = s;
+    }
+    __syncthreads();
+    for (int e = t; e < n * n; e += kT) {
+        const int a = e / n, b = e - a * n;
+        if (b < a) c.L[a * c.ldl + b] = c.L[b * c.ldl + a];
+        else if (a == b) c.L[a * c.ldl + a] = c.part[a];
+    }
+    __syncthreads();
+}
+
+// b := Minv b with Minv (symmetric) in c.L. Thread (g, i): columns g, g + ng, ...
+__device__ void minv_apply(const Ctx& c, double* b) {
+    const int n = c.n;
+    const int ng = kT / n;
+    const int g = threadIdx.x / n, i = threadIdx.x - g * n;
+    if (g < ng) {
+        double s = 0.0;
+        for (int j = g; j < n; j += ng) s = fma(c.L[j * c.ldl + i], b[j], s);
+        c.part[threadIdx.x] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < n) {
+        double s = 0.0;
+        for (int gg = 0; gg < ng; ++gg) s += c.part[gg * n + threadIdx.x];
+        b[threadIdx.x] = s;
+    }
+    __syncthreads();
+}
+
 // b := (L L')^-1 b, warp 0 only (the other warps wait at the barrier). Rows are dealt to lanes
 // round-robin (row i -> lane i & 31, slot i >> 5); the pivot value travels by shuffle.
 __device__ void chol_solve(const Ctx& c, double* b) {
@@ -527,6 +584,7 @@ __global__ void __launch_bounds__(kT) dense_qp_kernel(const DenseParams p) {
         bool have_x = false;
         int iter = 0;
         bool fact_ok = factorize(c, rv, p.sigma);
+        if (fact_ok) invert_factor(c);
         if (!fact_ok) status = MPCCBF_STATUS_ERROR;
         PolishBuf pb;
         pb.xk = xk; pb.rhs = rhs; pb.tn = tn; pb.q = q;
@@ -543,7 +601,7 @@ __global__ void __launch_bounds__(kT) dense_qp_kernel(const DenseParams p) {
             if (m > 0) mat_tvec(c, w, rhs);
             if (t < n) rhs[t] = (m > 0 ? rhs[t] : 0.0) + fma(p.sigma, x[t], -q[t]);
             __syncthreads();
-            chol_solve(c, rhs);  // rhs now holds x~
+            minv_apply(c, rhs);  // rhs now holds x~
             if (m > 0) mat_vec(c, rhs, zt, a_sm);
             if (t < n) {
                 const double xn = fma(p.alpha, rhs[t], (1.0 - p.alpha) * x[t]);
@@ -605,6 +663,7 @@ __global__ void __launch_bounds__(kT) dense_qp_kernel(const DenseParams p) {
                 }
                 if (iter == p.max_iter) break;
                 fact_ok = factorize(c, rv, p.sigma);  // polish overwrote the cached factor
+                if (fact_ok) invert_factor(c);
                 if (!fact_ok) {
                     status = MPCCBF_STATUS_ERROR;
                     break;
@@ -668,6 +727,7 @@ __global__ void __launch_bounds__(kT) dense_qp_kernel(const DenseParams p) {
                     rho = nr;
                     set_rho(rho);
                     fact_ok = factorize(c, rv, p.sigma);
+                    if (fact_ok) invert_factor(c);
                     if (!fact_ok) status = MPCCBF_STATUS_ERROR;
                 }
             }
