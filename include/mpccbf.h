@@ -219,6 +219,27 @@ int mpccbf_run_episode(mpccbf_handle* h, int32_t num_scenarios, double* states, 
                        int32_t* success, int32_t* finish_step, double* min_dist, int32_t* failed_calls,
                        double* traj, void* cuda_stream);
 
+/* Options of mpccbf_run_episode_ex. */
+#define MPCCBF_ORDER_JACOBI 0        /* every agent optimises on the same snapshot (one launch per step)   */
+#define MPCCBF_ORDER_GAUSS_SEIDEL 1  /* the reference's loop order (MPCCBFFormationControl_example.cpp:140):
+                                        agent i optimises and advances before agent i + 1 optimises        */
+typedef struct mpccbf_episode_opts {
+    double goal_radius;       /* reach_goal_area radius                                               */
+    double collision_radius;  /* robot_params.collision_shape.radius                                   */
+    int32_t order;            /* MPCCBF_ORDER_*                                                        */
+    double pos_std, vel_std;  /* mpc_params-level state noise of the driver (math::addRandomNoise,
+                                 math/src/Random.cpp:7-29: N(0, std) on every position / velocity
+                                 component at every sub-step); 0 = noise-free                          */
+    uint64_t seed;            /* the reference draws from random_device; here the noise is a
+                                 counter-based stream of (seed, scenario, agent, sub-step)             */
+} mpccbf_episode_opts;
+
+/* Same as mpccbf_run_episode with the loop order and the state noise of the reference driver. */
+int mpccbf_run_episode_ex(mpccbf_handle* h, int32_t num_scenarios, double* states, const double* targets,
+                          int32_t num_control_steps, const mpccbf_episode_opts* opts, int32_t* success,
+                          int32_t* finish_step, double* min_dist, int32_t* failed_calls, double* traj,
+                          void* cuda_stream);
+
 /* Sub-kernel K3: advance every agent along its curve by one MPC step, i.e. the state after the
  * h/Ts rollout sub-steps of MPCCBFFormationControl_example.cpp:191-205 without noise:
  * next[S][N][6] = (curve(h), curve'(h)); agents whose n_curves == 0 keep their position with zero

@@ -33,6 +33,7 @@ EXPORTED_SYMBOLS = [
     "mpccbf_last_iteration_counts", "mpccbf_copy_iteration_counts", "mpccbf_measure_fp64_tflops", "mpccbf_get_table",
     "mpccbf_linear_cost", "mpccbf_get_counters", "mpccbf_host_alloc", "mpccbf_host_free",
     "mpccbf_cbf_filter_batch", "mpccbf_cbf_filter_batch_host", "mpccbf_conn_rows", "mpccbf_run_episode",
+    "mpccbf_run_episode_ex",
 ]
 
 
@@ -69,6 +70,15 @@ class Config(C.Structure):
     @property
     def n(self):
         return self.num_pieces * 3 * self.num_ctrl_pts
+
+
+class EpisodeOpts(C.Structure):
+    """Mirror of `mpccbf_episode_opts` (include/mpccbf.h)."""
+    _fields_ = [("goal_radius", C.c_double), ("collision_radius", C.c_double), ("order", C.c_int32),
+                ("pos_std", C.c_double), ("vel_std", C.c_double), ("seed", C.c_uint64)]
+
+
+ORDER_JACOBI, ORDER_GAUSS_SEIDEL = 0, 1
 
 
 class MpcCbfError(RuntimeError):
@@ -122,6 +132,7 @@ def lib(path=None):
     L.mpccbf_cbf_filter_batch_host.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     L.mpccbf_conn_rows.argtypes = [vp, i32, vp, vp, vp, vp]
     L.mpccbf_run_episode.argtypes = [vp, i32, vp, vp, i32, dbl, dbl, vp, vp, vp, vp, vp, vp]
+    L.mpccbf_run_episode_ex.argtypes = [vp, i32, vp, vp, i32, C.POINTER(EpisodeOpts), vp, vp, vp, vp, vp, vp]
     L.mpccbf_rollout_agents.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp]
     L.mpccbf_last_iteration_counts.argtypes = [vp]
     L.mpccbf_last_iteration_counts.restype = vp
@@ -298,11 +309,18 @@ class Handle:
                                                     _ptr(lambda2), stream))
 
     def run_episode(self, S, states, targets, steps, goal_radius, collision_radius, success=None, finish_step=None,
-                    min_dist=None, failed_calls=None, traj=None, stream=None):
+                    min_dist=None, failed_calls=None, traj=None, stream=None, order=ORDER_JACOBI, pos_std=0.0,
+                    vel_std=0.0, seed=0):
         """Closed-loop episode on the device (states is updated in place); see include/mpccbf.h."""
-        self._check(self._L.mpccbf_run_episode(self._h, S, _ptr(states), _ptr(targets), steps, goal_radius,
-                                               collision_radius, _ptr(success), _ptr(finish_step), _ptr(min_dist),
-                                               _ptr(failed_calls), _ptr(traj), stream))
+        if order == ORDER_JACOBI and pos_std == 0.0 and vel_std == 0.0:
+            self._check(self._L.mpccbf_run_episode(self._h, S, _ptr(states), _ptr(targets), steps, goal_radius,
+                                                   collision_radius, _ptr(success), _ptr(finish_step), _ptr(min_dist),
+                                                   _ptr(failed_calls), _ptr(traj), stream))
+            return
+        o = EpisodeOpts(goal_radius, collision_radius, order, pos_std, vel_std, seed)
+        self._check(self._L.mpccbf_run_episode_ex(self._h, S, _ptr(states), _ptr(targets), steps, C.byref(o),
+                                                  _ptr(success), _ptr(finish_step), _ptr(min_dist),
+                                                  _ptr(failed_calls), _ptr(traj), stream))
 
     def conn_rows(self, S, states, rows, lambda2=None, stream=None):
         self._check(self._L.mpccbf_conn_rows(self._h, S, _ptr(states), _ptr(rows), _ptr(lambda2), stream))

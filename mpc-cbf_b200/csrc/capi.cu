@@ -42,7 +42,7 @@ struct mpccbf_handle {
     double *o_states = nullptr, *o_ref = nullptr, *o_ctrl = nullptr, *o_all = nullptr;
     int32_t* o_status = nullptr;
     // episode driver workspaces (allocated on first use)
-    double *e_curve = nullptr, *e_evalt = nullptr, *e_mind2 = nullptr, *e_ctrl = nullptr;
+    double *e_curve = nullptr, *e_evalt = nullptr, *e_mind2 = nullptr, *e_ctrl = nullptr, *e_sub = nullptr, *e_tg = nullptr;
     int32_t *e_has = nullptr, *e_done = nullptr, *e_finish = nullptr, *e_failed = nullptr, *e_status = nullptr, *e_nc = nullptr;
     unsigned char* e_reached = nullptr;
     int64_t launches = 0, qps = 0;
@@ -383,7 +383,7 @@ int mpccbf_destroy(mpccbf_handle* h) {
     if (!h) return MPCCBF_OK;
     if (h->has_device) {
         cudaSetDevice(h->device);
-        void* eptrs[] = {h->e_curve, h->e_ctrl, h->e_evalt, h->e_has, h->e_nc, h->e_status, h->e_reached, h->e_mind2,
+        void* eptrs[] = {h->e_sub, h->e_tg, h->e_curve, h->e_ctrl, h->e_evalt, h->e_has, h->e_nc, h->e_status, h->e_reached, h->e_mind2,
                          h->e_done, h->e_finish, h->e_failed};
         for (void* q : eptrs)
             if (q) cudaFree(q);
@@ -656,12 +656,13 @@ int mpccbf_conn_rows(mpccbf_handle* h, int32_t S, const double* states, double* 
     return MPCCBF_OK;
 }
 
-int mpccbf_run_episode(mpccbf_handle* h, int32_t S, double* states, const double* targets, int32_t steps, double goal_radius,
-                       double collision_radius, int32_t* success, int32_t* finish_step, double* min_dist, int32_t* failed_calls,
-                       double* traj, void* cuda_stream) {
+int mpccbf_run_episode_ex(mpccbf_handle* h, int32_t S, double* states, const double* targets, int32_t steps,
+                          const mpccbf_episode_opts* opts, int32_t* success, int32_t* finish_step, double* min_dist,
+                          int32_t* failed_calls, double* traj, void* cuda_stream) {
     int rc = require_device(h);
     if (rc != MPCCBF_OK) return rc;
-    if (S < 0 || S > h->cfg.max_scenarios || steps < 0 || !states || !targets) {
+    if (S < 0 || S > h->cfg.max_scenarios || steps < 0 || !states || !targets || !opts ||
+        (opts->order != MPCCBF_ORDER_JACOBI && opts->order != MPCCBF_ORDER_GAUSS_SEIDEL) || opts->pos_std < 0 || opts->vel_std < 0) {
         set_error("mpccbf_run_episode: invalid argument (num_scenarios must be <= max_scenarios)");
         return MPCCBF_ERR_INVALID;
     }
@@ -673,11 +674,14 @@ int mpccbf_run_episode(mpccbf_handle* h, int32_t S, double* states, const double
     CUDA_TRY(cudaSetDevice(h->device));
     cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
     const size_t B = static_cast<size_t>(h->cfg.max_scenarios) * h->cfg.num_agents, n = h->tab.n, it = h->cfg.impc_iter;
+    const int nsub = static_cast<int>(h->cfg.h / h->cfg.Ts);  // int(h / Ts), MPCCBFFormationControl_example.cpp:193
     if (!h->e_curve) {
         bool ok = true;
         ok &= cudaMalloc(&h->e_curve, sizeof(double) * B * n) == cudaSuccess;
         ok &= cudaMalloc(&h->e_ctrl, sizeof(double) * B * n) == cudaSuccess;
         ok &= cudaMalloc(&h->e_evalt, sizeof(double) * B) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_sub, sizeof(double) * B * std::max(nsub, 1) * 2) == cudaSuccess;
+        ok &= cudaMalloc(&h->e_tg, sizeof(double) * h->cfg.max_scenarios * 3) == cudaSuccess;
         ok &= cudaMalloc(&h->e_has, sizeof(int32_t) * B) == cudaSuccess;
         ok &= cudaMalloc(&h->e_nc, sizeof(int32_t) * B) == cudaSuccess;
         ok &= cudaMalloc(&h->e_status, sizeof(int32_t) * B * it) == cudaSuccess;
@@ -697,11 +701,13 @@ int mpccbf_run_episode(mpccbf_handle* h, int32_t S, double* states, const double
     a.states = states; a.targets = targets; a.ctrl_new = h->e_ctrl; a.n_curves = h->e_nc;
     a.curve = h->e_curve; a.eval_t = h->e_evalt; a.has_curve = h->e_has; a.reached = h->e_reached;
     a.done = h->e_done; a.finish = h->e_finish; a.min_dist2 = h->e_mind2; a.failed = h->e_failed; a.traj = traj;
+    a.sub = h->e_sub;
     a.S = S; a.N = N; a.n = h->tab.n; a.c = h->tab.c; a.p = h->tab.p; a.iters = h->cfg.impc_iter;
-    a.nsub = static_cast<int>(h->cfg.h / h->cfg.Ts);  // int(h / Ts), MPCCBFFormationControl_example.cpp:193
+    a.nsub = nsub;
     a.traj_len = steps * a.nsub;
     a.Ts = h->cfg.Ts; a.piece_T = h->cfg.piece_max_param;
-    a.goal_radius = goal_radius; a.collision_radius = collision_radius;
+    a.goal_radius = opts->goal_radius; a.collision_radius = opts->collision_radius;
+    a.pos_std = opts->pos_std; a.vel_std = opts->vel_std; a.seed = opts->seed;
     double cum = 0.0;
     for (int i = 0; i < 16; ++i) {
         if (i < h->tab.p) cum += h->cfg.piece_max_param;  // cumulative ends by repeated addition, like the reference
@@ -709,15 +715,39 @@ int mpccbf_run_episode(mpccbf_handle* h, int32_t S, double* states, const double
     }
     a.max_param = cum;
     for (int step = 0; step < steps; ++step) {
-        rc = run_step(h, S, 0, N, states, targets, 0, h->e_ctrl, nullptr, h->e_status, h->e_nc, nullptr, h->w_iters, st);
-        if (rc != MPCCBF_OK) return rc;
         a.step = step;
-        CUDA_TRY(launch_episode_advance(a, h->sm_count, st));
-        h->launches += 1;
+        if (opts->order == MPCCBF_ORDER_JACOBI) {
+            rc = run_step(h, S, 0, N, states, targets, 0, h->e_ctrl, nullptr, h->e_status, h->e_nc, nullptr, h->w_iters, st);
+            if (rc != MPCCBF_OK) return rc;
+            a.agent_begin = 0; a.agent_count = N; a.do_metrics = 1;
+            CUDA_TRY(launch_episode_advance(a, h->sm_count, st));
+            h->launches += 1;
+        } else {
+            for (int ag = 0; ag < N; ++ag) {
+                CUDA_TRY(launch_gather_agent_targets(S, N, ag, targets, h->e_tg, st));
+                rc = run_step(h, S, ag, 1, states, h->e_tg, 0, h->e_ctrl, nullptr, h->e_status, h->e_nc, nullptr, h->w_iters, st);
+                if (rc != MPCCBF_OK) return rc;
+                a.agent_begin = ag; a.agent_count = 1; a.do_metrics = (ag == N - 1) ? 1 : 0;
+                CUDA_TRY(launch_episode_advance(a, h->sm_count, st));
+                h->launches += 2;
+            }
+        }
     }
     CUDA_TRY(launch_episode_final(S, steps * a.nsub, h->e_done, h->e_finish, h->e_mind2, success, finish_step, min_dist, st));
     if (failed_calls) CUDA_TRY(cudaMemcpyAsync(failed_calls, h->e_failed, sizeof(int32_t) * S, cudaMemcpyDeviceToDevice, st));
     return MPCCBF_OK;
+}
+
+int mpccbf_run_episode(mpccbf_handle* h, int32_t S, double* states, const double* targets, int32_t steps, double goal_radius,
+                       double collision_radius, int32_t* success, int32_t* finish_step, double* min_dist, int32_t* failed_calls,
+                       double* traj, void* cuda_stream) {
+    mpccbf_episode_opts o;
+    o.goal_radius = goal_radius;
+    o.collision_radius = collision_radius;
+    o.order = MPCCBF_ORDER_JACOBI;
+    o.pos_std = o.vel_std = 0.0;
+    o.seed = 0;
+    return mpccbf_run_episode_ex(h, S, states, targets, steps, &o, success, finish_step, min_dist, failed_calls, traj, cuda_stream);
 }
 
 int mpccbf_rollout(mpccbf_handle* h, int32_t S, const double* states, const double* ctrl_pts,

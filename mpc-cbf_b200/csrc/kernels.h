@@ -56,13 +56,19 @@ struct EpisodeArgs {
     double* min_dist2;         // [S]
     int32_t* failed;           // [S] optimize calls that did not return all IMPC iterates (may be NULL)
     double* traj;              // [S][N][traj_len][6] or NULL
+    double* sub;               // [S][N][nsub][2] x/y of this control step's sub-steps (scratch)
     int S, N, n, c, p, iters, nsub, step, traj_len;
+    int agent_begin, agent_count;  // phase A range; ctrl_new / n_curves are [S][agent_count][..]
+    int do_metrics;            // phase B
     double Ts, piece_T, max_param, goal_radius, collision_radius;
+    double pos_std, vel_std;   // Gaussian state noise per sub-step (0: none)
+    unsigned long long seed;
     double cum[16];            // cumulative piece ends
 };
 int launch_episode_init(int S, int N, double* eval_t, int32_t* has_curve, unsigned char* reached, int32_t* done, int32_t* finish,
                         double* min_dist2, int32_t* failed, cudaStream_t stream);
 int launch_episode_advance(const EpisodeArgs& a, int sm_count, cudaStream_t stream);
+int launch_gather_agent_targets(int S, int N, int agent, const double* targets, double* out, cudaStream_t stream);
 int launch_episode_final(int S, int total_substeps, const int32_t* done, const int32_t* finish, const double* min_dist2,
                          int32_t* success, int32_t* finish_step, double* min_dist, cudaStream_t stream);
 struct DenseOpts {

@@ -28,7 +28,7 @@ def instance_success(traj, goals, radius, coll_radius):
     return True, T
 
 
-def run(M, cfg, st, tg, steps, goal_r, coll_r):
+def run(M, cfg, st, tg, steps, goal_r, coll_r, **kw):
     import torch
     S, N = st.shape[:2]
     h = M.Handle(cfg)
@@ -37,7 +37,8 @@ def run(M, cfg, st, tg, steps, goal_r, coll_r):
     out = dict(success=torch.zeros(S, dtype=torch.int32, device="cuda"), finish=torch.zeros(S, dtype=torch.int32, device="cuda"),
                min_dist=torch.zeros(S, dtype=torch.float64, device="cuda"), failed=torch.zeros(S, dtype=torch.int32, device="cuda"),
                traj=torch.zeros((S, N, steps * nsub, 6), dtype=torch.float64, device="cuda"))
-    h.run_episode(S, d_st, d_tg, steps, goal_r, coll_r, out["success"], out["finish"], out["min_dist"], out["failed"], out["traj"])
+    h.run_episode(S, d_st, d_tg, steps, goal_r, coll_r, out["success"], out["finish"], out["min_dist"], out["failed"], out["traj"],
+                  **kw)
     torch.cuda.synchronize()
     res = {k: v.cpu().numpy() for k, v in out.items()}
     res["final"] = d_st.cpu().numpy()
@@ -122,3 +123,81 @@ def test_episode_two_robot_config(M):
     assert res["traj"].shape == (1, 2, 2000, 6)
     assert res["failed"][0] > 0          # the exact head-on swap has infeasible steps
     h.close()
+
+
+def test_episode_gauss_seidel_matches_host_driver(M, tmp_path):
+    # the reference's loop order: the host driver (formation_example --mode gauss_seidel, one optimize_one call
+    # per robot) and the device episode in MPCCBF_ORDER_GAUSS_SEIDEL must produce the same states.json
+    import json
+    import subprocess
+    from conftest import ROOT
+    host = os.path.join(ROOT, "mpc-cbf_b200", "host")
+    subprocess.run(["make", "-C", host], check=True, stdout=subprocess.DEVNULL)
+    out = tmp_path / "gs.json"
+    r = subprocess.run([os.path.join(host, "formation_example"), "--config_file", os.path.join(GOLDEN, "circle2_config.json"),
+                        "--write_filename", str(out), "--sim_runtime", "20", "--mode", "gauss_seidel"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    js = json.load(open(out))
+    ref = np.array([js["robots"][str(i)]["states"] for i in range(2)])[:, :2000]     # [2][2000][6]
+    assert ref.shape == (2, 2000, 6)
+    cfg, so, sf = M.config_from_json(os.path.join(GOLDEN, "circle2_config.json"), max_scenarios=1)
+    st = np.zeros((1, 2, 6))
+    st[0, :, :3] = so[:2]
+    h, res = run(M, cfg, st, sf[None, :2, :].copy(), 200, 1.0, 0.3, order=M.ORDER_GAUSS_SEIDEL)
+    assert np.abs(res["traj"][0] - ref).max() < 1e-6
+    h.close()
+
+
+def test_episode_gauss_seidel_matches_oracle(M, O):
+    # a pulled-in 4-agent swarm where safety rows bind: the Gauss-Seidel episode against the oracle stepped
+    # robot by robot (robot i optimises on the states robots < i have already advanced to), and it must
+    # differ from the Jacobi episode
+    S, N, steps = 1, 4, 10
+    cfg = M.default_config(k_hor=16, num_pieces=3, d_min=0.8, num_agents=N, max_scenarios=S)
+    from parity import dense_scenarios
+    st, tg = dense_scenarios(S, N, 3, 0.8, spread=1.2, vmax=1.0)
+    h, gs = run(M, cfg, st, tg, steps, 1.0, 0.2, order=M.ORDER_GAUSS_SEIDEL)
+    h2, jac = run(M, cfg, st, tg, steps, 1.0, 0.2)
+    assert np.abs(gs["traj"] - jac["traj"]).max() > 1e-4
+    oc = O.base_config(k_hor=16, num_pieces=3, d_min=0.8, num_agents=N)
+    s = st[0].copy()
+    prev, et = [None] * N, np.zeros(N)
+    for step in range(steps):
+        for a in range(N):
+            r = O.optimize(oc, s, a, np.tile(tg[0, a], 16), prec=1)
+            if r["n_curves"] > 0:
+                prev[a], et[a] = r["curves"][-1].copy(), 0.0
+            for ti in range(1, 11):
+                if prev[a] is None:
+                    s[a, 3:] = 0.0
+                else:
+                    t = min(et[a] + 0.01 * ti, 1.5)
+                    s[a, :3] = O.eval_curve(oc, prev[a], t, 0)
+                    s[a, 3:] = O.eval_curve(oc, prev[a], t, 1)
+                assert np.abs(gs["traj"][0, a, 10 * step + ti - 1] - s[a]).max() < 1e-6, (step, a, ti)
+            et[a] = min(et[a] + 0.1, 1.5)
+    h.close()
+    h2.close()
+
+
+def test_episode_noise_statistics(M):
+    # seeded N(0, std) on every component at every sub-step (math::addRandomNoise): deterministic per seed,
+    # right moments on the first control step (where the clean trajectory is the same)
+    S, N = 64, 8
+    cfg = M.default_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N, max_scenarios=S)
+    st, tg = swarm(S, N, seed=2)
+    h0, clean = run(M, cfg, st, tg, 1, 1.0, 0.2)
+    h1, n1 = run(M, cfg, st, tg, 1, 1.0, 0.2, pos_std=0.01, vel_std=0.05, seed=123)
+    h2, n2 = run(M, cfg, st, tg, 1, 1.0, 0.2, pos_std=0.01, vel_std=0.05, seed=123)
+    h3, n3 = run(M, cfg, st, tg, 1, 1.0, 0.2, pos_std=0.01, vel_std=0.05, seed=124)
+    assert np.array_equal(n1["traj"], n2["traj"]) and not np.array_equal(n1["traj"], n3["traj"])
+    d = n1["traj"] - clean["traj"]            # [S][N][10][6]
+    for sl, std in ((slice(0, 3), 0.01), (slice(3, 6), 0.05)):
+        x = d[..., sl].ravel() / std
+        assert abs(x.mean()) < 4 / np.sqrt(x.size) and abs(x.std() - 1.0) < 0.03
+        assert abs(np.mean(x ** 4) - 3.0) < 0.3                 # Gaussian kurtosis
+    # components and sub-steps are uncorrelated
+    c = np.corrcoef(d[..., 0].ravel(), d[..., 1].ravel())[0, 1]
+    assert abs(c) < 0.05
+    for h in (h0, h1, h2, h3):
+        h.close()
