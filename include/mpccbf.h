@@ -141,6 +141,15 @@ int mpccbf_step_batch_host(mpccbf_handle* h, int32_t num_scenarios, const double
                            const double* targets, double* ctrl_pts, int32_t* status,
                            int32_t* n_curves, double* objective);
 
+/* Split form of the call above for callers that pipeline batches: _async returns once the copies and
+ * the launch are enqueued on the handle's own streams (pageable buffers may make it block), the
+ * buffers must stay untouched until mpccbf_synchronize(h) returns. Two handles used alternately
+ * overlap the PCIe phase of one batch with the solve of the next (bench.py's e2e leg does). */
+int mpccbf_step_batch_host_async(mpccbf_handle* h, int32_t num_scenarios, const double* states,
+                                 const double* targets, double* ctrl_pts, int32_t* status,
+                                 int32_t* n_curves, double* objective);
+int mpccbf_synchronize(mpccbf_handle* h);
+
 /* Single-agent drop-in for S-ctl (host pointers): states [N][6], ref [3*k_hor] (only used as a
  * per-step reference: ref[3k..3k+2] is the target at horizon step k), ctrl_pts [impc_iter][n]
  * receives EVERY successful iterate in order (result_curves), *n_curves how many,

@@ -33,7 +33,7 @@ EXPORTED_SYMBOLS = [
     "mpccbf_last_iteration_counts", "mpccbf_copy_iteration_counts", "mpccbf_measure_fp64_tflops", "mpccbf_get_table",
     "mpccbf_linear_cost", "mpccbf_get_counters", "mpccbf_host_alloc", "mpccbf_host_free",
     "mpccbf_cbf_filter_batch", "mpccbf_cbf_filter_batch_host", "mpccbf_conn_rows", "mpccbf_run_episode",
-    "mpccbf_run_episode_ex",
+    "mpccbf_run_episode_ex", "mpccbf_step_batch_host_async", "mpccbf_synchronize",
 ]
 
 
@@ -123,6 +123,8 @@ def lib(path=None):
     L.mpccbf_active_solver.argtypes = [vp]
     L.mpccbf_step_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, vp]
     L.mpccbf_step_batch_host.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+    L.mpccbf_step_batch_host_async.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+    L.mpccbf_synchronize.argtypes = [vp]
     L.mpccbf_step_agents.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
     L.mpccbf_optimize_one.argtypes = [vp, vp, i32, vp, vp, vp, vp]
     L.mpccbf_solve_qp_dense.argtypes = [vp, i32, i32, i32] + [vp] * 11
@@ -253,6 +255,16 @@ class Handle:
                                                    _ptr(out["ctrl_pts"]), _ptr(out["status"]),
                                                    _ptr(out["n_curves"]), _ptr(out["objective"])))
         return out
+
+    def step_batch_host_async(self, states, targets, out):
+        """Enqueue only (buffers must be contiguous float64 / int32 arrays that outlive synchronize())."""
+        S = states.shape[0]
+        self._check(self._L.mpccbf_step_batch_host_async(self._h, S, states.ctypes.data, targets.ctypes.data,
+                                                         _ptr(out["ctrl_pts"]), _ptr(out["status"]),
+                                                         _ptr(out["n_curves"]), _ptr(out["objective"])))
+
+    def synchronize(self):
+        self._check(self._L.mpccbf_synchronize(self._h))
 
     def cbf_filter_batch_host(self, states, desired_u):
         """cbf::ConnectivityControl::optimize for every agent: dict(u [S][N][3], status [S][N], lambda2 [S])."""

@@ -106,6 +106,17 @@ def test_device_pointer_step_rollout_and_agent_shards(M, O, torch):
     h.step_batch_host(pst.numpy(), ptg.numpy(), out={k: v.numpy() for k, v in pinned.items()})
     for k in pinned:
         assert np.array_equal(pinned[k].numpy(), host[k]), k
+    # split form: enqueue on two handles, then synchronise both (what bench.py's pipelined e2e leg does)
+    h_b = M.Handle(cfg)
+    pinned_b = {k: torch.zeros_like(v).pin_memory() for k, v in pinned.items()}
+    pinned["ctrl_pts"].fill_(float("nan"))
+    h.step_batch_host_async(pst.numpy(), ptg.numpy(), {k: v.numpy() for k, v in pinned.items()})
+    h_b.step_batch_host_async(pst.numpy(), ptg.numpy(), {k: v.numpy() for k, v in pinned_b.items()})
+    h.synchronize()
+    h_b.synchronize()
+    for k in pinned:
+        assert np.array_equal(pinned[k].numpy(), host[k]) and np.array_equal(pinned_b[k].numpy(), host[k]), k
+    h_b.close()
     # agent-sharded launch: two halves reproduce the whole
     for begin, cnt in ((0, 8), (8, 8), (5, 3)):
         cp2 = torch.zeros((S, cnt, h.n), dtype=torch.float64, device="cuda")
