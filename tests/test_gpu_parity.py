@@ -135,3 +135,26 @@ def test_edge_cases(M, O, torch_cuda):
     with pytest.raises(M.MpcCbfError):
         h.step_batch_host(np.zeros((9, 1, 6)), np.zeros((9, 1, 3)))
     h.close()
+
+
+def test_one_sided_limits_and_single_agent(M, O, torch_cuda):
+    # (i) a velocity limit of 1e30 ("no bound" for CPLEX) disables the key scan of the thread kernel
+    # (it needs finite two-sided bounds): the step falls back to the lane-group kernel and must still
+    # agree with the oracle on a batch large enough for the throughput path; (ii) N = 1: no neighbours
+    S, N = 320, 16
+    cfg = north_star_cfg(M, num_agents=N, max_scenarios=S, v_max=[2.0, 1e30, 2.6])
+    h = M.Handle(cfg)
+    st, tg = dense_scenarios(S, N, 21, 0.8, spread=2.5, vmax=1.5)
+    got = h.step_batch_host(st, tg)
+    oc = ocfg_of(O, cfg)
+    r = check_step(O, oc, O.get_table(oc, "U_basis"), st[:24], tg[:24], {k: v[:24] for k, v in got.items()}, check_viol_max=8)
+    assert r["n_infeasible"] < 24 * N
+    h.close()
+    cfg = north_star_cfg(M, num_agents=1, max_scenarios=8)
+    h = M.Handle(cfg)
+    st, tg = swarm(8, 1, seed=4)
+    got = h.step_batch_host(st, tg)
+    oc = ocfg_of(O, cfg)
+    check_step(O, oc, O.get_table(oc, "U_basis"), st, tg, got)
+    assert (got["status"] == 0).all()
+    h.close()
