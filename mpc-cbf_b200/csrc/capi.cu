@@ -257,9 +257,16 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
     int lanes = h->lanes;
-    if (lanes < 0)  // throughput kernel for real batches, lane groups (lower latency) for tiny ones
-        lanes = (a.num_qp >= 32 * h->sm_count) ? 0 : (a.num_qp >= 4 * h->sm_count ? 8 : 32);
-    if (lanes == 0 && !h->dev.poly) lanes = 8;  // the thread kernel needs the polynomial row structure
+    if (lanes < 0) {
+        // Measured crossover on B200 (profiles/r1h_kernel_crossover.md): a warp per agent (32 lanes split
+        // the row scan) wins while all its warps fit in one wave of 8 per SM — twice that for dense swarms,
+        // where a scan walks hundreds of safety rows; the thread-per-agent kernel wins beyond. The 8-lane
+        // variant is only the large-batch fallback for configurations without the polynomial row structure.
+        const int wave = 8 * h->sm_count * (h->cfg.num_agents >= 128 ? 2 : 1);
+        lanes = (a.num_qp <= wave) ? 32 : 0;
+    }
+    if (lanes == 0 && !h->dev.poly)  // the thread kernel needs the polynomial row structure
+        lanes = (a.num_qp >= 2048 && h->cfg.num_agents < 64) ? 8 : 32;
     if (lanes == 0)
         CUDA_TRY(launch_impc_thread(h->dev, a, h->sm_count, stream));
     else
