@@ -45,6 +45,9 @@ struct mpccbf_handle {
     double *e_curve = nullptr, *e_evalt = nullptr, *e_mind2 = nullptr, *e_ctrl = nullptr, *e_sub = nullptr, *e_tg = nullptr;
     int32_t *e_has = nullptr, *e_done = nullptr, *e_finish = nullptr, *e_failed = nullptr, *e_status = nullptr, *e_nc = nullptr;
     unsigned char* e_reached = nullptr;
+    // slack-mode controller path: reduced (6 + N-1)-variable QPs through the dense kernel (slack_path.cu)
+    bool slack_reduced = false;
+    SlackWorkspace sw;
     int64_t launches = 0, qps = 0;
 };
 
@@ -238,9 +241,9 @@ int build_device_tables(mpccbf_handle* h) {
 int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_count, const double* states,
              const double* targets, int ref_mode, double* ctrl, double* ctrl_all, int32_t* status,
              int32_t* n_curves, double* objective, int32_t* iters, cudaStream_t stream) {
-    if (h->solver != MPCCBF_SOLVER_REDUCED) {
+    if (h->solver != MPCCBF_SOLVER_REDUCED && !h->slack_reduced) {
         set_error("controller path: this configuration does not reduce to the 6-dof form (needs cubic pieces with "
-                  "C^3 continuity and slack_mode = false); use mpccbf_solve_qp_dense for the assembled QP");
+                  "C^3 continuity); use mpccbf_solve_qp_dense for the assembled QP");
         return MPCCBF_ERR_UNSUPPORTED;
     }
     StepArgs a;
@@ -256,6 +259,19 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
     a.agent_begin = agent_begin;
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
+    if (h->slack_reduced) {
+        DenseOpts o;
+        o.max_iter = h->cfg.admm_max_iter;
+        o.check_every = h->cfg.admm_check_every;
+        o.eps = h->cfg.admm_eps;
+        o.rho = h->cfg.admm_rho;
+        o.sigma = h->cfg.admm_sigma;
+        o.sm_count = h->sm_count;
+        o.stream = stream;
+        const int rc = slack_step(h->dev, h->cfg, a, o, h->sw, &h->launches);
+        if (rc == MPCCBF_OK) h->qps += static_cast<int64_t>(a.num_qp) * h->cfg.impc_iter;
+        return rc;
+    }
     int lanes = h->lanes;
     if (lanes < 0) {
         // Measured crossover on B200 (profiles/r1h_kernel_crossover.md): a warp per agent (32 lanes split
@@ -320,6 +336,9 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
         return MPCCBF_ERR_UNSUPPORTED;
     }
     h->solver = (cfg->solver == MPCCBF_SOLVER_DENSE || !can_reduce) ? MPCCBF_SOLVER_DENSE : MPCCBF_SOLVER_REDUCED;
+    // slack mode keeps the null-space reduction of the equality rows but not the strictly convex solver
+    h->slack_reduced = h->cfg.slack_mode && h->tab.reducible && h->tab.r1 == 2 && h->cfg.num_agents >= 1 &&
+                       cfg->solver != MPCCBF_SOLVER_REDUCED;
     if (const char* env = std::getenv("MPCCBF_LANES")) {
         const int w = std::atoi(env);
         if (w == 32 || w == 8 || w == 1 || w == 0) h->lanes = w;
@@ -394,6 +413,7 @@ int mpccbf_destroy(mpccbf_handle* h) {
                          h->e_done, h->e_finish, h->e_failed};
         for (void* q : eptrs)
             if (q) cudaFree(q);
+        slack_free(h->sw);
         void* ptrs[] = {h->d_tmpl, h->d_yw, h->d_vr, h->d_kr, h->w_states, h->w_targets, h->w_ctrl, h->w_obj,
                         h->w_status, h->w_ncurves, h->w_iters, h->o_states, h->o_ref, h->o_ctrl, h->o_all, h->o_status};
         for (void* p : ptrs)

@@ -592,6 +592,7 @@ __global__ void __launch_bounds__(kT) dense_qp_kernel(const DenseParams p) {
         // NOTE: polish borrows w (weights), zt (rhs weights) and dy (A xk); the ADMM loop rebuilds
         // w and zt every iteration and dy is only read at check iterations after being rewritten.
         int since_polish = 0;
+        int polish_gap = 2 * p.check_every;
         while (fact_ok && iter < p.max_iter) {
             ++iter;
             const bool check = (iter % p.check_every) == 0 || iter == p.max_iter;
@@ -643,8 +644,9 @@ __global__ void __launch_bounds__(kT) dense_qp_kernel(const DenseParams p) {
             const bool converged = rp <= p.eps + p.eps * np_ && rd <= p.eps + p.eps * nd;
             since_polish += p.check_every;
             const bool loose = rp <= 1e-2 * (1.0 + np_) && rd <= 1e-2 * (1.0 + nd);
-            if (converged || (loose && since_polish >= 2 * p.check_every) || iter == p.max_iter) {
+            if (converged || (loose && since_polish >= polish_gap) || iter == p.max_iter) {
                 since_polish = 0;
+                polish_gap = min(2 * polish_gap, 64 * p.check_every);  // a failed attempt costs ~100 iterations: back off
                 if (t < n) xk[t] = x[t];
                 __syncthreads();
                 int rounds = 0;
@@ -761,6 +763,66 @@ __global__ void __launch_bounds__(kT) dense_qp_kernel(const DenseParams p) {
         }                                                                           \
     } while (0)
 
+// Launch geometry and solver settings shared by the host- and device-pointer entries.
+static bool plan_launch(const DenseOpts& o, int batch, int n, int mt, DenseParams& p, SmemPlan& pl) {
+    p.n = n; p.m = mt; p.batch = batch;
+    p.lda = n | 1;
+    p.ldl = n | 1;
+    pl = plan_smem(n, mt, p.lda, p.ldl, true);
+    p.a_in_smem = pl.bytes <= 200 * 1024 ? 1 : 0;
+    if (!p.a_in_smem) pl = plan_smem(n, mt, p.lda, p.ldl, false);
+    if (pl.bytes > 227 * 1024) return false;
+    p.max_iter = o.max_iter > 0 ? o.max_iter : 20000;
+    p.check_every = o.check_every > 0 ? o.check_every : 10;
+    p.ruiz_iters = 15;
+    p.eps = o.eps > 0 ? o.eps : 1e-7;
+    p.rho0 = o.rho > 0 ? o.rho : 0.1;
+    p.sigma = o.sigma > 0 ? o.sigma : 1e-6;
+    p.alpha = 1.6;
+    p.eps_inf = 1e-5;
+    return true;
+}
+
+static int launch_kernel(const DenseOpts& o, const DenseParams& p, const SmemPlan& pl) {
+    cudaError_t e = cudaFuncSetAttribute(dense_qp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.bytes));
+    int per_sm = 1;
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dense_qp_kernel, kT, pl.bytes);
+    if (e == cudaSuccess) {
+        // one CTA per QP: iteration counts vary by 100x between QPs, so the hardware block scheduler
+        // balances the SMs instead of a static grid-stride assignment
+        (void)per_sm;
+        dense_qp_kernel<<<p.batch, kT, pl.bytes, o.stream>>>(p);
+        e = cudaGetLastError();
+    }
+    if (e != cudaSuccess) {
+        set_error(std::string("dense_qp_kernel launch: ") + cudaGetErrorString(e));
+        return MPCCBF_ERR_CUDA;
+    }
+    return MPCCBF_OK;
+}
+
+// Device-pointer entry: QPs already assembled in HBM (slack_path.cu). Bytes of per-QP scratch the
+// caller provides: wsP n*n doubles, wsA m*(n|1) doubles when dense_qp_needs_wsA says so.
+bool dense_qp_needs_wsA(int n, int m) {
+    const SmemPlan pl = plan_smem(n, m, n | 1, n | 1, true);
+    return pl.bytes > 200 * 1024;
+}
+
+int dense_qp_solve_device(const DenseOpts& o, int32_t batch, int32_t n, int32_t m, const double* P, const double* q,
+                          const double* A, const double* l, const double* u, double* wsP, double* wsA, double* x,
+                          double* objective, int32_t* status, int32_t* iters) {
+    if (batch == 0) return MPCCBF_OK;
+    DenseParams p;
+    SmemPlan pl;
+    if (n > kMaxN || !plan_launch(o, batch, n, m, p, pl)) {
+        set_error("dense QP kernel: more than 128 variables or too many rows for one CTA's shared memory");
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    p.P = P; p.q = q; p.A = A; p.l = l; p.u = u;
+    p.wsP = wsP; p.wsA = wsA; p.x = x; p.obj = objective; p.status = status; p.iters = iters;
+    return launch_kernel(o, p, pl);
+}
+
 // Host-pointer entry (mpccbf_solve_qp_dense). Variable bounds become identity rows.
 int dense_qp_solve_host(const DenseOpts& o, int32_t batch, int32_t n, int32_t m, const double* P,
                         const double* q, const double* A, const double* l, const double* u,
@@ -806,24 +868,11 @@ int dense_qp_solve_host(const DenseOpts& o, int32_t batch, int32_t n, int32_t m,
         uh = ux.data();
     }
     DenseParams p;
-    p.n = n; p.m = mt; p.batch = batch;
-    p.lda = n | 1;
-    p.ldl = n | 1;
-    SmemPlan pl = plan_smem(n, mt, p.lda, p.ldl, true);
-    p.a_in_smem = pl.bytes <= 200 * 1024 ? 1 : 0;
-    if (!p.a_in_smem) pl = plan_smem(n, mt, p.lda, p.ldl, false);
-    if (pl.bytes > 227 * 1024) {
+    SmemPlan pl;
+    if (!plan_launch(o, batch, n, mt, p, pl)) {
         set_error("mpccbf_solve_qp_dense: too many rows for the shared-memory vectors of one CTA");
         return MPCCBF_ERR_UNSUPPORTED;
     }
-    p.max_iter = o.max_iter > 0 ? o.max_iter : 20000;
-    p.check_every = o.check_every > 0 ? o.check_every : 10;
-    p.ruiz_iters = 15;
-    p.eps = o.eps > 0 ? o.eps : 1e-7;
-    p.rho0 = o.rho > 0 ? o.rho : 0.1;
-    p.sigma = o.sigma > 0 ? o.sigma : 1e-6;
-    p.alpha = 1.6;
-    p.eps_inf = 1e-5;
     int rc = MPCCBF_OK;
     double *dP = nullptr, *dq = nullptr, *dA = nullptr, *dl = nullptr, *du = nullptr, *dwP = nullptr, *dwA = nullptr,
            *dx = nullptr, *dobj = nullptr;
@@ -851,12 +900,8 @@ int dense_qp_solve_host(const DenseOpts& o, int32_t batch, int32_t n, int32_t m,
         }
         p.P = dP; p.q = dq; p.A = dA; p.l = dl; p.u = du;
         p.wsP = dwP; p.wsA = dwA; p.x = dx; p.obj = dobj; p.status = dst; p.iters = dit;
-        DQ_TRY(cudaFuncSetAttribute(dense_qp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.bytes)));
-        int per_sm = 1;
-        DQ_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dense_qp_kernel, kT, pl.bytes));
-        const int grid = std::min<int>(batch, std::max(1, per_sm) * std::max(1, o.sm_count));
-        dense_qp_kernel<<<grid, kT, pl.bytes, st>>>(p);
-        DQ_TRY(cudaGetLastError());
+        rc = launch_kernel(o, p, pl);
+        if (rc != MPCCBF_OK) goto done;
         DQ_TRY(cudaMemcpyAsync(x, dx, sizeof(double) * B * n, cudaMemcpyDeviceToHost, st));
         DQ_TRY(cudaMemcpyAsync(status, dst, sizeof(int32_t) * B, cudaMemcpyDeviceToHost, st));
         if (objective) DQ_TRY(cudaMemcpyAsync(objective, dobj, sizeof(double) * B, cudaMemcpyDeviceToHost, st));

@@ -81,6 +81,23 @@ int dense_qp_solve_host(const DenseOpts& opts, int32_t batch, int32_t n, int32_t
                         const double* q, const double* A, const double* l, const double* u,
                         const double* lb, const double* ub, double* x, double* objective,
                         int32_t* status, int32_t* iters);
+bool dense_qp_needs_wsA(int n, int m);
+int dense_qp_solve_device(const DenseOpts& opts, int32_t batch, int32_t n, int32_t m, const double* P, const double* q,
+                          const double* A, const double* l, const double* u, double* wsP, double* wsA, double* x,
+                          double* objective, int32_t* status, int32_t* iters);
+
+// Slack-mode controller path (slack_path.cu): reduced (6 + N-1)-variable QPs assembled on the device
+// and solved by the dense kernel. The workspace belongs to the handle and grows on demand.
+struct SlackWorkspace {
+    size_t cap_qps = 0;     // QPs the buffers below hold
+    int nv = 0, m_max = 0;  // shape they were sized for
+    double *P = nullptr, *q = nullptr, *A = nullptr, *l = nullptr, *u = nullptr, *wsP = nullptr, *wsA = nullptr;
+    double *x = nullptr, *obj = nullptr, *pred = nullptr, *vlast = nullptr, *objlast = nullptr, *c0 = nullptr;
+    int32_t *stat = nullptr, *it = nullptr, *nok = nullptr;
+};
+int slack_step(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, const DenseOpts& o, SlackWorkspace& w,
+               int64_t* launches);
+void slack_free(SlackWorkspace& w);
 void set_error(const std::string& msg);
 #ifdef MPCCBF_HOST_EMUL
 void emul_impc_reduced_host(const DevTables& T, const StepArgs& a);

@@ -1,0 +1,80 @@
+"""GPU parity of the slack-mode controller path (cbf_params.slack_mode = true,
+ConnectivityIMPCCBF.cpp:76-100, MPCCBFQPGeneratorBase.cpp:28-38,80-135) against the oracle's
+full-space restatement: same status, control points and objective through mpccbf_step_batch_host."""
+import numpy as np
+import pytest
+
+from conftest import swarm
+from parity import TOL_CONTROL, check_step, dense_scenarios
+
+pytestmark = pytest.mark.gpu
+
+
+def cfgs(M, O, N, S, **kw):
+    base = dict(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N, slack_mode=1, slack_cost=50000.0, slack_decay=0.1)
+    base.update(kw)
+    return M.default_config(max_scenarios=S, **base), O.base_config(**base)
+
+
+@pytest.mark.parametrize("N,S,seed", [(2, 6, 1), (5, 6, 2), (8, 4, 3), (16, 3, 4)])
+def test_slack_step_matches_oracle(M, O, N, S, seed):
+    # packed swarms: without slack about half of these QPs are infeasible; with slack every one is
+    # solved and the far neighbours' rows (weights down to 5e4 * 0.1^(N-2)) are effectively soft
+    cfg, oc = cfgs(M, O, N, S)
+    h = M.Handle(cfg)
+    assert h.solver == M.SOLVER_DENSE
+    st, tg = dense_scenarios(S, N, seed, 0.8, spread=1.15, vmax=1.0)
+    got = h.step_batch_host(st, tg)
+    U = O.get_table(oc, "U_basis")
+    res = check_step(O, oc, U, st, tg, got, check_viol_max=0)
+    assert (got["n_curves"] == 2).all()  # slack makes every packed case feasible
+    print(f"slack N={N}: {S * N * 2} QPs, control-point error {res['err_x']:.2e}")
+    h.close()
+
+
+def test_slack_equals_hard_rows_when_no_row_binds_beyond_its_weight(M, O):
+    # well separated ring: the slack optimum is the hard-constrained one (s = 0)
+    N, S = 8, 4
+    cfg, oc = cfgs(M, O, N, S)
+    hard = M.default_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N, max_scenarios=S)
+    st, tg = swarm(S, N, seed=11)
+    hs, hh = M.Handle(cfg), M.Handle(hard)
+    a, b = hs.step_batch_host(st, tg), hh.step_batch_host(st, tg)
+    assert np.array_equal(a["status"], b["status"]) and (a["n_curves"] == 2).all()
+    assert np.abs(a["ctrl_pts"] - b["ctrl_pts"]).max() <= TOL_CONTROL
+    hs.close()
+    hh.close()
+
+
+def test_slack_infeasible_bound_rows_and_closed_loop(M, O):
+    # slack softens only the safety rows: an initial speed beyond v_max still reports INFEASIBLE and
+    # the later iterate SKIPPED (same bookkeeping as the hard path); then a short closed loop
+    N, S = 4, 2
+    cfg, oc = cfgs(M, O, N, S)
+    h = M.Handle(cfg)
+    st, tg = dense_scenarios(S, N, 5, 0.8, spread=1.4, vmax=0.5)
+    st[0, 1, 3] = 2.6  # v_max = 2
+    U = O.get_table(oc, "U_basis")
+    got = h.step_batch_host(st, tg)
+    check_step(O, oc, U, st, tg, got, check_viol_max=0)
+    assert list(got["status"][0, 1]) == [M.STATUS_INFEASIBLE, M.STATUS_SKIPPED] and got["n_curves"][0, 1] == 0
+    st[0, 1, 3] = 0.3
+    for _ in range(5):
+        got = h.step_batch_host(st, tg)
+        check_step(O, oc, U, st, tg, got, check_viol_max=0)
+        for s in range(S):
+            for a in range(N):
+                if got["n_curves"][s, a] > 0:
+                    st[s, a, :3] = O.eval_curve(oc, got["ctrl_pts"][s, a], cfg.h, 0)
+                    st[s, a, 3:] = O.eval_curve(oc, got["ctrl_pts"][s, a], cfg.h, 1)
+    h.close()
+
+
+def test_slack_too_many_neighbours_is_an_error(M):
+    cfg = M.default_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=130, max_scenarios=1, slack_mode=1,
+                           slack_cost=50000.0, slack_decay=0.1)
+    h = M.Handle(cfg)
+    st = np.zeros((1, 130, 6)); st[0, :, 0] = np.arange(130) * 2.0
+    with pytest.raises(M.MpcCbfError):
+        h.step_batch_host(st, np.zeros((1, 130, 3)))
+    h.close()
