@@ -73,7 +73,10 @@ typedef struct mpccbf_config {
     double d_min, d_max;      /* cbf_params.d_min / d_max                               */
     double cbf_gamma;         /* 5.0 in the reference                                   */
     int32_t impc_iter;        /* cbf_params.impc_iter                                   */
-    int32_t slack_mode;       /* cbf_params.slack_mode                                  */
+    int32_t slack_mode;       /* cbf_params.slack_mode: one slack >= 0 per neighbour on its
+                               * safety rows (ConnectivityIMPCCBF.cpp:76-100); controller
+                               * entries then run assemble -> ADMM kernel -> finish on the
+                               * device (num_agents - 1 <= 122), see DESIGN.md section 8      */
     double slack_cost;        /* cbf_params.slack_cost                                  */
     double slack_decay;       /* cbf_params.slack_decay_rate                            */
     int32_t num_agents;       /* robots per scenario (tasks.so length)                  */
@@ -117,7 +120,10 @@ const char* mpccbf_version(void);
 /* Decision-vector length n = num_pieces*3*num_ctrl_pts, layout x[piece*3c + axis*c + cp]
  * (BezierQPOperations.cpp:37, PiecewiseBezierMPCQPGenerator.cpp:9-34). */
 int32_t mpccbf_num_decision_vars(const mpccbf_handle* h);
-/* Which solver the controller path resolved to (MPCCBF_SOLVER_REDUCED / _DENSE). */
+/* Which solver the controller path resolved to: MPCCBF_SOLVER_REDUCED (fused active-set kernels) or
+ * MPCCBF_SOLVER_DENSE (ADMM kernel: slack mode on the reduced QPs; for configurations that do not
+ * reduce at all only mpccbf_solve_qp_dense is available and the controller entries return
+ * MPCCBF_ERR_UNSUPPORTED). */
 int32_t mpccbf_active_solver(const mpccbf_handle* h);
 
 /* Batched control step == ConnectivityIMPCCBF::optimize for every agent of every scenario

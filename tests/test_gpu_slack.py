@@ -78,3 +78,27 @@ def test_slack_too_many_neighbours_is_an_error(M):
     with pytest.raises(M.MpcCbfError):
         h.step_batch_host(st, np.zeros((1, 130, 3)))
     h.close()
+
+
+def test_slack_episode_on_the_device_follows_the_hard_episode_when_no_slack_is_used(M, O):
+    # the episode driver goes through the same controller step: on separated swarms the slack-mode
+    # closed loop must retrace the hard-constrained one. ADMM with exact-penalty weights of 5e4 can run
+    # out of iterations on a close encounter (reported as UNKNOWN, counted in failed_calls, never as
+    # OPTIMAL - DESIGN.md section 8); scenarios where that happened are excluded from the comparison.
+    import torch
+    N, S, steps = 4, 6, 12
+    cfg, _ = cfgs(M, O, N, S)
+    hard = M.default_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N, max_scenarios=S)
+    st, tg = swarm(S, N, seed=21)
+    out = []
+    for c in (cfg, hard):
+        h = M.Handle(c)
+        d_st, d_tg = torch.tensor(st, device="cuda"), torch.tensor(tg, device="cuda")
+        failed = torch.zeros(S, dtype=torch.int32, device="cuda")
+        h.run_episode(S, d_st, d_tg, steps, 0.3, 0.3, failed_calls=failed)
+        torch.cuda.synchronize()
+        out.append((d_st.cpu().numpy(), failed.cpu().numpy()))
+        h.close()
+    clean = (out[0][1] == 0) & (out[1][1] == 0)
+    assert clean.sum() >= S - 1, (out[0][1], out[1][1])
+    assert np.abs(out[0][0] - out[1][0])[clean].max() <= 1e-6
