@@ -307,6 +307,13 @@ int mpccbf_linear_cost(const mpccbf_handle* h, const double* x0, const double* r
 void* mpccbf_host_alloc(size_t bytes);
 void mpccbf_host_free(void* p);
 
+/* Slack mode runs in two tiers: the fused hard-row kernels first, then a per-agent KKT check of whether
+ * that optimum is also the slack-mode optimum (every safety multiplier within its weight); agents that
+ * fail the check - hard QP infeasible, a cap exceeded, degenerate active set - are re-solved with the
+ * slack variables by the ADMM kernel. Returns the cumulative number of agent-steps that took the second
+ * tier on this handle (-1 for a NULL handle). */
+int64_t mpccbf_slack_fallback_count(const mpccbf_handle* h);
+
 /* Counters since create (may be NULL individually). */
 int mpccbf_get_counters(const mpccbf_handle* h, int64_t* kernel_launches, int64_t* qps_solved);
 

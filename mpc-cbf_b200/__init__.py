@@ -33,7 +33,7 @@ EXPORTED_SYMBOLS = [
     "mpccbf_last_iteration_counts", "mpccbf_copy_iteration_counts", "mpccbf_measure_fp64_tflops", "mpccbf_get_table",
     "mpccbf_linear_cost", "mpccbf_get_counters", "mpccbf_host_alloc", "mpccbf_host_free",
     "mpccbf_cbf_filter_batch", "mpccbf_cbf_filter_batch_host", "mpccbf_conn_rows", "mpccbf_run_episode",
-    "mpccbf_run_episode_ex", "mpccbf_step_batch_host_async", "mpccbf_synchronize",
+    "mpccbf_run_episode_ex", "mpccbf_step_batch_host_async", "mpccbf_synchronize", "mpccbf_slack_fallback_count",
 ]
 
 
@@ -121,6 +121,8 @@ def lib(path=None):
     L.mpccbf_version.restype = C.c_char_p
     L.mpccbf_num_decision_vars.argtypes = [vp]
     L.mpccbf_active_solver.argtypes = [vp]
+    L.mpccbf_slack_fallback_count.argtypes = [vp]
+    L.mpccbf_slack_fallback_count.restype = C.c_int64
     L.mpccbf_step_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, vp]
     L.mpccbf_step_batch_host.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
     L.mpccbf_step_batch_host_async.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
@@ -344,6 +346,10 @@ class Handle:
     def rollout_agents(self, S, agent_count, states, ctrl_pts, n_curves, next_states, stream=None):
         self._check(self._L.mpccbf_rollout_agents(self._h, S, agent_count, _ptr(states), _ptr(ctrl_pts),
                                                   _ptr(n_curves), _ptr(next_states), stream))
+
+    def slack_fallback_count(self):
+        """Agent-steps of this handle that needed the slack variables (second tier), cumulative."""
+        return int(self._L.mpccbf_slack_fallback_count(self._h))
 
     def last_iteration_counts_ptr(self):
         return self._L.mpccbf_last_iteration_counts(self._h)

@@ -94,9 +94,22 @@ struct SlackWorkspace {
     double *P = nullptr, *q = nullptr, *A = nullptr, *l = nullptr, *u = nullptr, *wsP = nullptr, *wsA = nullptr;
     double *x = nullptr, *obj = nullptr, *pred = nullptr, *vlast = nullptr, *objlast = nullptr, *c0 = nullptr;
     int32_t *stat = nullptr, *it = nullptr, *nok = nullptr;
+    // first tier (hard-row solve + verification): iterates of the fused kernels, agents for the ADMM tier
+    size_t hard_cap = 0;
+    double* hard_all = nullptr;   // [hard_cap][iters][n]
+    int32_t* list = nullptr;      // [hard_cap]
+    int32_t* count = nullptr;     // device counter
+    int32_t* h_count = nullptr;   // pinned host copy
 };
+// ADMM tier for the QPs in `list` (device array of `count` QP indices), or for all of `a` when list is NULL.
 int slack_step(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, const DenseOpts& o, SlackWorkspace& w,
-               int64_t* launches);
+               const int32_t* list, int count, int64_t* launches);
+// Buffers of the first tier for `num_qp` agents; then, after the fused hard-row kernels ran with
+// ctrl_all = a.ctrl_all, the verification: fills w.list and returns the number of agents in *n_fallback
+// (synchronises the stream).
+int slack_prepare_hard(const DevTables& T, int num_qp, SlackWorkspace& w);
+int slack_verify(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, SlackWorkspace& w, int sm_count,
+                 cudaStream_t stream, int* n_fallback);
 void slack_free(SlackWorkspace& w);
 void set_error(const std::string& msg);
 #ifdef MPCCBF_HOST_EMUL

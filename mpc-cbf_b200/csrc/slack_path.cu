@@ -32,7 +32,8 @@ struct SlackLaunch {
     const double* states;
     const double* targets;
     int ref_mode;
-    int g0, count;  // QP range [g0, g0 + count) of the StepArgs batch handled by this chunk
+    int g0, count;  // entries [g0, g0 + count) of `list` (or QPs g0.. themselves when list is NULL)
+    const int32_t* list;
     int agent_begin, agent_count;
     int it, hit, nv, m, J;
     double slack_cost, slack_decay;
@@ -57,6 +58,23 @@ __device__ __forceinline__ void safety_hocbf(double px, double py, double vx, do
     b = lf2h + lfa + gamma * psi1 * psi1 * psi1;
 }
 
+// slack_cost * slack_decay^rank, rank of neighbour j among the J neighbours by distance to the ego agent
+// (closest first, ties by index; ConnectivityIMPCCBF.cpp:76-100)
+__device__ double slack_weight(const double* st, int self, int j, int J, double cost, double decay) {
+    const double* me = st + self * 6;
+    const int other = j + (j >= self ? 1 : 0);
+    const double dx = st[other * 6] - me[0], dy = st[other * 6 + 1] - me[1];
+    const double dj = sqrt(dx * dx + dy * dy);
+    int rank = 0;
+    for (int i = 0; i < J; ++i) {
+        const int oi = i + (i >= self ? 1 : 0);
+        const double ex = st[oi * 6] - me[0], ey = st[oi * 6 + 1] - me[1];
+        const double di = sqrt(ex * ex + ey * ey);
+        rank += (di < dj || (di == dj && i < j)) ? 1 : 0;
+    }
+    return cost * pow(decay, static_cast<double>(rank));
+}
+
 // One CTA per QP. Row order: safety rows (neighbour-major, horizon step inside), acceleration bound
 // rows [k][axis], velocity bound rows [k][axis], slack >= 0 rows.
 __global__ void __launch_bounds__(kTA) slack_assemble_kernel(const DevTables T, const SlackLaunch a) {
@@ -64,7 +82,7 @@ __global__ void __launch_bounds__(kTA) slack_assemble_kernel(const DevTables T, 
     const int K = T.K, N = T.N, J = a.J, nv = a.nv, m = a.m, hit = a.hit, t = threadIdx.x;
     const double* tm = T.tmpl;
     for (int b = blockIdx.x; b < a.count; b += gridDim.x) {
-        const int g = a.g0 + b;
+        const int g = a.list ? a.list[a.g0 + b] : a.g0 + b;
         const int scen = g / a.agent_count;
         const int self = a.agent_begin + (g - scen * a.agent_count);
         __syncthreads();
@@ -113,17 +131,7 @@ __global__ void __launch_bounds__(kTA) slack_assemble_kernel(const DevTables T, 
         }
         // ---- slack weights by distance rank (ConnectivityIMPCCBF.cpp:76-100) and s_j >= 0 rows -------
         for (int j = t; j < J; j += kTA) {
-            const int other = j + (j >= self ? 1 : 0);
-            const double dx = st[other * 6] - me[0], dy = st[other * 6 + 1] - me[1];
-            const double dj = sqrt(dx * dx + dy * dy);
-            int rank = 0;
-            for (int i = 0; i < J; ++i) {
-                const int oi = i + (i >= self ? 1 : 0);
-                const double ex = st[oi * 6] - me[0], ey = st[oi * 6 + 1] - me[1];
-                const double di = sqrt(ex * ex + ey * ey);
-                rank += (di < dj || (di == dj && i < j)) ? 1 : 0;
-            }
-            q[6 + j] = a.slack_cost * pow(a.slack_decay, static_cast<double>(rank));
+            q[6 + j] = slack_weight(st, self, j, J, a.slack_cost, a.slack_decay);
             const int r = J * hit + 6 * K + j;
             A[static_cast<size_t>(r) * nv + 6 + j] = 1.0;
             l[r] = 0.0;
@@ -182,6 +190,7 @@ __global__ void __launch_bounds__(kTA) slack_assemble_kernel(const DevTables T, 
 
 struct SlackFinish {
     const double* states;
+    const int32_t* list;
     int g0, count, agent_begin, agent_count, it, nv;
     int m, hit, J;
     const double *x, *c0, *A, *u, *q;  // the assembled QP of this iteration (rows: see slack_assemble_kernel)
@@ -201,7 +210,7 @@ __global__ void __launch_bounds__(kTA) slack_finish_kernel(const DevTables T, co
     const int lane = threadIdx.x & 31;
     const int warps = (gridDim.x * kTA) >> 5;
     for (int b = (blockIdx.x * kTA + threadIdx.x) >> 5; b < a.count; b += warps) {
-        const int g = a.g0 + b;
+        const int g = a.list ? a.list[a.g0 + b] : a.g0 + b;
         const int scen = g / a.agent_count;
         const int self = a.agent_begin + (g - scen * a.agent_count);
         const double* me = a.states + (static_cast<size_t>(scen) * T.N + self) * 6;
@@ -290,6 +299,203 @@ __global__ void __launch_bounds__(kTA) slack_finish_kernel(const DevTables T, co
     }
 }
 
+// ---- first tier: is the hard-row optimum already the slack-mode optimum? --------------------------------
+// The slack QP min 1/2|v - v0|^2 + sum_j w_j s_j has the same minimiser as the hard-row QP (with s = 0) iff
+// the hard optimum's multipliers on neighbour j's safety rows sum to at most w_j (KKT of the slack QP with
+// mu_j = w_j - sum_k lambda_jk >= 0 on s_j >= 0). One warp per agent re-derives, per IMPC iterate of the
+// fused hard-row kernels, the active x/y rows at the returned point, solves the <= 4-column least-squares
+// system v0 - v = sum_i lambda_i n_i, and accepts the agent when stationarity holds to 1e-7, lambda >= 0 and
+// every cap holds with margin. Everything else (infeasible hard QP, a cap exceeded, degenerate or more
+// than 4 active rows) goes to the ADMM tier through `list`.
+struct SlackVerify {
+    const double* states;
+    const double* targets;
+    int ref_mode;
+    int num_qp, agent_begin, agent_count;
+    double slack_cost, slack_decay;
+    const double* ctrl_all;  // [B][iters][n] iterates of the hard-row solve
+    const int32_t* status;   // [B][iters]
+    int32_t* list;
+    int32_t* count;
+};
+constexpr int kVW = 4;  // warps per CTA
+
+__global__ void __launch_bounds__(kVW * 32) slack_verify_kernel(const DevTables T, const SlackVerify a) {
+    extern __shared__ double vsm[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int N = T.N, K = T.K, J = N - 1, m1 = T.m1;
+    double* st = vsm + static_cast<size_t>(wib) * (N * 6 + 24);
+    double* nrm = st + N * 6;                      // [4][4] active normals
+    int* nbi = reinterpret_cast<int*>(nrm + 16);   // [4] neighbour of a soft row, -1 for a bound row
+    const double* tm = T.tmpl;
+    const double tol = 1e-8;
+    const int nwarps = gridDim.x * kVW;
+    for (int g = blockIdx.x * kVW + wib; g < a.num_qp; g += nwarps) {
+        const int scen = g / a.agent_count;
+        const int self = a.agent_begin + (g - scen * a.agent_count);
+        __syncwarp();
+        for (int i = lane; i < N * 6; i += 32) st[i] = __ldg(a.states + static_cast<size_t>(scen) * N * 6 + i);
+        __syncwarp();
+        const double* me = st + self * 6;
+        bool pass = true;
+        double vprev[6] = {0, 0, 0, 0, 0, 0};
+        for (int it = 0; it < T.iters && pass; ++it) {
+            if (a.status[static_cast<size_t>(g) * T.iters + it] != MPCCBF_STATUS_OPTIMAL) {
+                pass = false;
+                break;
+            }
+            // whitened free dof of this iterate from its control points, and v0 of the x / y axes
+            const double* x = a.ctrl_all + (static_cast<size_t>(g) * T.iters + it) * T.n;
+            double mine = 0.0, mine0 = 0.0;
+            if (lane < 6) {
+                const int ax = lane >> 1, r = lane & 1;
+                for (int i = 0; i < m1; ++i)
+                    mine = fma(T.gv[r * m1 + i], x[(i / T.c) * 3 * T.c + ax * T.c + (i % T.c)], mine);
+                mine -= T.gv[2 * m1 + 2 * r] * me[ax] + T.gv[2 * m1 + 2 * r + 1] * me[3 + ax];
+                double rr = 0.0;
+                if (a.ref_mode == 0) {
+                    rr = T.Vt[r] * __ldg(a.targets + static_cast<size_t>(g) * 3 + ax);
+                } else {
+                    const double* rf = a.targets + static_cast<size_t>(g) * 3 * K;
+                    for (int k = 0; k < K; ++k) rr = fma(T.Vr[r * K + k], __ldg(rf + 3 * k + ax), rr);
+                }
+                mine0 = T.Vs[r][0] * me[ax] + T.Vs[r][1] * me[3 + ax] + rr;
+            }
+            double v[6], r4[4];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) v[c] = __shfl_sync(0xffffffffu, mine, c);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) r4[c] = __shfl_sync(0xffffffffu, mine0, c) - v[c];
+            // ---- active x / y rows at v ------------------------------------------------------------------
+            const int hit = it == 0 ? 1 : T.H;
+            const int total = 4 * K + J * hit;
+            int cnt = 0;
+            for (int base = 0; base < total; base += 32) {
+                const int e = base + lane;
+                bool active = false;
+                double n4[4] = {0, 0, 0, 0};
+                int nb = -1;
+                if (e < 4 * K) {
+                    const int dsel = e >= 2 * K ? 1 : 0;
+                    const int rr = e - dsel * 2 * K;
+                    const int k = rr >> 1, ax = rr & 1;
+                    const double* tk = tm + ((2 - dsel) * K + k) * kTmplStride;
+                    if (tk[0] != 0.0 || tk[1] != 0.0) {
+                        const double val = tk[0] * v[2 * ax] + tk[1] * v[2 * ax + 1] + tk[2] * me[ax] + tk[3] * me[3 + ax];
+                        const double lo = T.lim_lo[dsel][ax], hi = T.lim_hi[dsel][ax];
+                        double sgn = 0.0;
+                        if (hi < 1e20 && fabs(val - hi) <= tol * (1.0 + fabs(hi))) sgn = 1.0;
+                        else if (lo > -1e20 && fabs(val - lo) <= tol * (1.0 + fabs(lo))) sgn = -1.0;
+                        if (sgn != 0.0) {
+                            active = true;
+                            n4[2 * ax] = sgn * tk[0];
+                            n4[2 * ax + 1] = sgn * tk[1];
+                        }
+                    }
+                } else if (e < total) {
+                    const int r = e - 4 * K;
+                    nb = r / hit;
+                    const int k = r - nb * hit;
+                    const int other = nb + (nb >= self ? 1 : 0);
+                    double px = me[0], py = me[1], vx = me[3], vy = me[4];
+                    if (it > 0) {  // predicted ego state at t_k from the previous iterate
+                        const double* t0 = tm + (0 * K + k) * kTmplStride;
+                        const double* t1 = tm + (1 * K + k) * kTmplStride;
+                        px = t0[0] * vprev[0] + t0[1] * vprev[1] + t0[2] * me[0] + t0[3] * me[3];
+                        py = t0[0] * vprev[2] + t0[1] * vprev[3] + t0[2] * me[1] + t0[3] * me[4];
+                        vx = t1[0] * vprev[0] + t1[1] * vprev[1] + t1[2] * me[0] + t1[3] * me[3];
+                        vy = t1[0] * vprev[2] + t1[1] * vprev[3] + t1[2] * me[1] + t1[3] * me[4];
+                    }
+                    const double* o = st + other * 6;
+                    double ax, ay, bb;
+                    safety_hocbf(px, py, vx, vy, o[0], o[1], o[3], o[4], T.dmin2, T.gamma, ax, ay, bb);
+                    const double* tk = tm + (2 * K + k) * kTmplStride;
+                    n4[0] = -ax * tk[0];
+                    n4[1] = -ax * tk[1];
+                    n4[2] = -ay * tk[0];
+                    n4[3] = -ay * tk[1];
+                    const double ub = bb + ax * (tk[2] * me[0] + tk[3] * me[3]) + ay * (tk[2] * me[1] + tk[3] * me[4]);
+                    const double val = n4[0] * v[0] + n4[1] * v[1] + n4[2] * v[2] + n4[3] * v[3];
+                    active = fabs(val - ub) <= tol * (1.0 + fabs(ub));
+                }
+                const unsigned bal = __ballot_sync(0xffffffffu, active);
+                const int slot = cnt + __popc(bal & ((1u << lane) - 1u));
+                if (active && slot < 4) {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) nrm[slot * 4 + c] = n4[c];
+                    nbi[slot] = nb;
+                }
+                cnt += __popc(bal);
+            }
+            __syncwarp();
+            if (cnt > 4) {
+                pass = false;
+                break;
+            }
+            // ---- multipliers: least squares on the active normals (every lane, same arithmetic) ----------
+            double G[4][4], rhs[4], lam[4] = {0, 0, 0, 0};
+            for (int i = 0; i < cnt; ++i) {
+                rhs[i] = nrm[i * 4] * r4[0] + nrm[i * 4 + 1] * r4[1] + nrm[i * 4 + 2] * r4[2] + nrm[i * 4 + 3] * r4[3];
+                for (int j = 0; j <= i; ++j)
+                    G[i][j] = nrm[i * 4] * nrm[j * 4] + nrm[i * 4 + 1] * nrm[j * 4 + 1] + nrm[i * 4 + 2] * nrm[j * 4 + 2] +
+                              nrm[i * 4 + 3] * nrm[j * 4 + 3];
+            }
+            for (int j = 0; j < cnt && pass; ++j) {  // Cholesky G = L L'
+                double d = G[j][j];
+                for (int k = 0; k < j; ++k) d -= G[j][k] * G[j][k];
+                if (!(d > 1e-10 * G[j][j])) {
+                    pass = false;  // dependent active normals: multipliers not unique
+                    break;
+                }
+                G[j][j] = sqrt(d);
+                for (int i = j + 1; i < cnt; ++i) {
+                    double s2 = G[i][j];
+                    for (int k = 0; k < j; ++k) s2 -= G[i][k] * G[j][k];
+                    G[i][j] = s2 / G[j][j];
+                }
+            }
+            if (!pass) break;
+            for (int i = 0; i < cnt; ++i) {
+                double s2 = rhs[i];
+                for (int k = 0; k < i; ++k) s2 -= G[i][k] * lam[k];
+                lam[i] = s2 / G[i][i];
+            }
+            for (int i = cnt - 1; i >= 0; --i) {
+                double s2 = lam[i];
+                for (int k = i + 1; k < cnt; ++k) s2 -= G[k][i] * lam[k];
+                lam[i] = s2 / G[i][i];
+            }
+            double rmax = 0.0, res = 0.0, lmax = 0.0;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                double e = r4[c];
+                for (int i = 0; i < cnt; ++i) e -= lam[i] * nrm[i * 4 + c];
+                res = fmax(res, fabs(e));
+                rmax = fmax(rmax, fabs(r4[c]));
+            }
+            for (int i = 0; i < cnt; ++i) lmax = fmax(lmax, fabs(lam[i]));
+            if (!(res <= 1e-7 * (1.0 + rmax))) pass = false;
+            for (int i = 0; i < cnt && pass; ++i) {
+                if (lam[i] < -1e-7 * (1.0 + lmax)) pass = false;
+                if (nbi[i] < 0) continue;
+                bool first = true;
+                double sum = 0.0;
+                for (int j = 0; j < cnt; ++j)
+                    if (nbi[j] == nbi[i]) {
+                        if (j < i) first = false;
+                        sum += fmax(lam[j], 0.0);
+                    }
+                if (first && !(sum <= (1.0 - 1e-6) * slack_weight(st, self, nbi[i], J, a.slack_cost, a.slack_decay)))
+                    pass = false;
+            }
+#pragma unroll
+            for (int c = 0; c < 6; ++c) vprev[c] = v[c];
+            __syncwarp();
+        }
+        if (!pass && lane == 0) a.list[atomicAdd(a.count, 1)] = g;
+    }
+}
+
 __global__ void slack_reset_kernel(int32_t* nok, double* vlast, int count) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) nok[i] = 0;
@@ -305,16 +511,67 @@ bool grow(P** ptr, size_t elems) {
 
 }  // namespace
 
-void slack_free(SlackWorkspace& w) {
+static void free_admm(SlackWorkspace& w) {  // the ADMM tier's buffers only (they are re-sized on demand)
     void* ptrs[] = {w.P, w.q, w.A, w.l, w.u, w.wsP, w.wsA, w.x, w.obj, w.pred, w.vlast, w.objlast, w.c0, w.stat, w.it, w.nok};
     for (void* p : ptrs)
         if (p) cudaFree(p);
+    w.P = w.q = w.A = w.l = w.u = w.wsP = w.wsA = w.x = w.obj = w.pred = w.vlast = w.objlast = w.c0 = nullptr;
+    w.stat = w.it = w.nok = nullptr;
+    w.cap_qps = 0;
+}
+
+int slack_prepare_hard(const DevTables& T, int num_qp, SlackWorkspace& w) {
+    if (w.hard_cap >= static_cast<size_t>(num_qp)) return MPCCBF_OK;
+    bool ok = grow(&w.hard_all, static_cast<size_t>(num_qp) * T.iters * T.n) && grow(&w.list, static_cast<size_t>(num_qp));
+    if (!w.count) ok = ok && grow(&w.count, 1);
+    if (!w.h_count) ok = ok && cudaMallocHost(reinterpret_cast<void**>(&w.h_count), sizeof(int32_t)) == cudaSuccess;
+    if (!ok) {
+        set_error("slack mode: device workspace allocation failed");
+        return MPCCBF_ERR_ALLOC;
+    }
+    w.hard_cap = num_qp;
+    return MPCCBF_OK;
+}
+
+int slack_verify(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, SlackWorkspace& w, int sm_count,
+                 cudaStream_t stream, int* n_fallback) {
+    SlackVerify V;
+    V.states = a.states; V.targets = a.targets; V.ref_mode = a.ref_mode;
+    V.num_qp = a.num_qp; V.agent_begin = a.agent_begin; V.agent_count = a.agent_count;
+    V.slack_cost = cfg.slack_cost; V.slack_decay = cfg.slack_decay;
+    V.ctrl_all = a.ctrl_all; V.status = a.status; V.list = w.list; V.count = w.count;
+    const size_t smem = sizeof(double) * kVW * (static_cast<size_t>(T.N) * 6 + 24);
+    cudaError_t e = cudaMemsetAsync(w.count, 0, sizeof(int32_t), stream);
+    if (e == cudaSuccess && smem > 48 * 1024)
+        e = cudaFuncSetAttribute(slack_verify_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e == cudaSuccess) {
+        const int grid = std::min((a.num_qp + kVW - 1) / kVW, 16 * std::max(1, sm_count));
+        slack_verify_kernel<<<grid, kVW * 32, smem, stream>>>(T, V);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(w.h_count, w.count, sizeof(int32_t), cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) {
+        set_error(std::string("slack verification: ") + cudaGetErrorString(e));
+        return MPCCBF_ERR_CUDA;
+    }
+    *n_fallback = *w.h_count;
+    return MPCCBF_OK;
+}
+
+void slack_free(SlackWorkspace& w) {
+    void* ptrs[] = {w.P, w.q, w.A, w.l, w.u, w.wsP, w.wsA, w.x, w.obj, w.pred, w.vlast, w.objlast, w.c0, w.stat, w.it, w.nok,
+                    w.hard_all, w.list, w.count};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    if (w.h_count) cudaFreeHost(w.h_count);
     w = SlackWorkspace();
 }
 
 // One control step of the slack-mode controller for the QPs of `a`, in chunks that fit the workspace.
 int slack_step(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, const DenseOpts& o, SlackWorkspace& w,
-               int64_t* launches) {
+               const int32_t* list, int list_count, int64_t* launches) {
+    const int total_qp = list ? list_count : a.num_qp;
     const int N = T.N, J = N - 1, H = std::max(1, static_cast<int>(T.H)), K = T.K, iters = T.iters;
     const int nv = 6 + J;
     const int m_max = J * H + 6 * K + J;
@@ -328,9 +585,9 @@ int slack_step(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, 
                                             H * 6 + 12) + 12;
     size_t cap_mb = 1536;
     if (const char* env = std::getenv("MPCCBF_SLACK_WS_MB")) cap_mb = std::max(1, std::atoi(env));
-    const size_t want = std::min<size_t>(a.num_qp, std::max<size_t>(1, (cap_mb << 20) / per_qp));
+    const size_t want = std::min<size_t>(total_qp, std::max<size_t>(1, (cap_mb << 20) / per_qp));
     if (w.cap_qps < want || w.nv != nv || w.m_max != m_max) {
-        slack_free(w);
+        free_admm(w);
         bool ok = true;
         ok &= grow(&w.P, want * nv * nv) && grow(&w.wsP, want * nv * nv) && grow(&w.A, want * m_max * nv);
         ok &= grow(&w.wsA, need_wsA ? want * m_max * (nv | 1) : 1);
@@ -338,7 +595,7 @@ int slack_step(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, 
         ok &= grow(&w.obj, want) && grow(&w.pred, want * H * 6) && grow(&w.vlast, want * 6) && grow(&w.objlast, want);
         ok &= grow(&w.c0, want * 3) && grow(&w.stat, want) && grow(&w.it, want) && grow(&w.nok, want);
         if (!ok) {
-            slack_free(w);
+            free_admm(w);
             set_error("slack mode: device workspace allocation failed (lower MPCCBF_SLACK_WS_MB)");
             return MPCCBF_ERR_ALLOC;
         }
@@ -347,15 +604,15 @@ int slack_step(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, 
         w.m_max = m_max;
     }
     cudaStream_t st = o.stream;
-    for (int g0 = 0; g0 < a.num_qp; g0 += static_cast<int>(w.cap_qps)) {
-        const int count = std::min<int>(static_cast<int>(w.cap_qps), a.num_qp - g0);
+    for (int g0 = 0; g0 < total_qp; g0 += static_cast<int>(w.cap_qps)) {
+        const int count = std::min<int>(static_cast<int>(w.cap_qps), total_qp - g0);
         slack_reset_kernel<<<(count * 6 + 255) / 256, 256, 0, st>>>(w.nok, w.vlast, count);
         for (int it = 0; it < iters; ++it) {
             const int hit = it == 0 ? 1 : H;
             const int m = J * hit + 6 * K + J;
             SlackLaunch L;
             L.states = a.states; L.targets = a.targets; L.ref_mode = a.ref_mode;
-            L.g0 = g0; L.count = count; L.agent_begin = a.agent_begin; L.agent_count = a.agent_count;
+            L.g0 = g0; L.count = count; L.list = list; L.agent_begin = a.agent_begin; L.agent_count = a.agent_count;
             L.it = it; L.hit = hit; L.nv = nv; L.m = m; L.J = J;
             L.slack_cost = cfg.slack_cost; L.slack_decay = cfg.slack_decay;
             L.P = w.P; L.q = w.q; L.A = w.A; L.l = w.l; L.u = w.u; L.c0 = w.c0;
@@ -369,7 +626,7 @@ int slack_step(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, 
             const int rc = dense_qp_solve_device(o, count, nv, m, w.P, w.q, w.A, w.l, w.u, w.wsP, w.wsA, w.x, w.obj, w.stat, w.it);
             if (rc != MPCCBF_OK) return rc;
             SlackFinish F;
-            F.states = a.states; F.g0 = g0; F.count = count; F.agent_begin = a.agent_begin; F.agent_count = a.agent_count;
+            F.states = a.states; F.list = list; F.g0 = g0; F.count = count; F.agent_begin = a.agent_begin; F.agent_count = a.agent_count;
             F.it = it; F.nv = nv; F.m = m; F.hit = hit; F.J = J; F.x = w.x; F.c0 = w.c0; F.A = w.A; F.u = w.u; F.q = w.q; F.dstat = w.stat; F.dit = w.it;
             F.pred = w.pred; F.vlast = w.vlast; F.objlast = w.objlast; F.nok = w.nok;
             F.ctrl_pts = a.ctrl_pts; F.ctrl_all = a.ctrl_all; F.objective = a.objective;

@@ -16,10 +16,14 @@ def cfgs(M, O, N, S, **kw):
     return M.default_config(max_scenarios=S, **base), O.base_config(**base)
 
 
+@pytest.mark.parametrize("fast", [1, 0])
 @pytest.mark.parametrize("N,S,seed", [(2, 6, 1), (5, 6, 2), (8, 4, 3), (16, 3, 4)])
-def test_slack_step_matches_oracle(M, O, N, S, seed):
+def test_slack_step_matches_oracle(M, O, N, S, seed, fast, monkeypatch):
     # packed swarms: without slack about half of these QPs are infeasible; with slack every one is
-    # solved and the far neighbours' rows (weights down to 5e4 * 0.1^(N-2)) are effectively soft
+    # solved and the far neighbours' rows (weights down to 5e4 * 0.1^(N-2)) are effectively soft.
+    # fast = 1: hard-row kernels + KKT verification first, ADMM only for the agents that need slack;
+    # fast = 0: every agent through the ADMM tier.
+    monkeypatch.setenv("MPCCBF_SLACK_FAST", str(fast))
     cfg, oc = cfgs(M, O, N, S)
     h = M.Handle(cfg)
     assert h.solver == M.SOLVER_DENSE
@@ -28,7 +32,9 @@ def test_slack_step_matches_oracle(M, O, N, S, seed):
     U = O.get_table(oc, "U_basis")
     res = check_step(O, oc, U, st, tg, got, check_viol_max=0)
     assert (got["n_curves"] == 2).all()  # slack makes every packed case feasible
-    print(f"slack N={N}: {S * N * 2} QPs, control-point error {res['err_x']:.2e}")
+    nfb = h.slack_fallback_count()
+    assert nfb == S * N if not fast else 0 < nfb < S * N or N == 2
+    print(f"slack N={N} fast={fast}: {S * N} agents, {nfb} through the ADMM tier, control-point error {res['err_x']:.2e}")
     h.close()
 
 
@@ -42,6 +48,7 @@ def test_slack_equals_hard_rows_when_no_row_binds_beyond_its_weight(M, O):
     a, b = hs.step_batch_host(st, tg), hh.step_batch_host(st, tg)
     assert np.array_equal(a["status"], b["status"]) and (a["n_curves"] == 2).all()
     assert np.abs(a["ctrl_pts"] - b["ctrl_pts"]).max() <= TOL_CONTROL
+    assert hs.slack_fallback_count() <= S * N // 4  # the KKT check keeps (nearly) every agent on the first tier
     hs.close()
     hh.close()
 
@@ -70,13 +77,20 @@ def test_slack_infeasible_bound_rows_and_closed_loop(M, O):
     h.close()
 
 
-def test_slack_too_many_neighbours_is_an_error(M):
+def test_slack_too_many_neighbours_is_an_error_only_when_slack_is_needed(M, monkeypatch):
+    # the first tier has no size limit; the ADMM tier holds 128 variables per CTA (6 + 122 slacks)
     cfg = M.default_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=130, max_scenarios=1, slack_mode=1,
                            slack_cost=50000.0, slack_decay=0.1)
     h = M.Handle(cfg)
     st = np.zeros((1, 130, 6)); st[0, :, 0] = np.arange(130) * 2.0
+    tg = st[:, :, :3] + np.array([0.0, 1.0, 0.0])
+    got = h.step_batch_host(st, tg)
+    assert (got["n_curves"] == 2).all() and h.slack_fallback_count() == 0
+    h.close()
+    monkeypatch.setenv("MPCCBF_SLACK_FAST", "0")
+    h = M.Handle(cfg)
     with pytest.raises(M.MpcCbfError):
-        h.step_batch_host(st, np.zeros((1, 130, 3)))
+        h.step_batch_host(st, tg)
     h.close()
 
 
