@@ -33,8 +33,8 @@ struct mpccbf_handle {
     int lanes = -1;  // lanes per agent-QP: 0 = thread-per-agent kernel, 8/32 = lane-group kernel, -1 = by batch size
     cudaStream_t stream = nullptr, stream2 = nullptr;
     // device copies of the tables
-    double *d_tmpl = nullptr, *d_yw = nullptr, *d_vr = nullptr, *d_kr = nullptr, *d_gv = nullptr;
-    std::vector<double> h_tmpl, h_yw, h_vr, h_kr, h_gv;  // host copies (uploaded at create)
+    double *d_tmpl = nullptr, *d_yw = nullptr, *d_vr = nullptr, *d_kr = nullptr;
+    std::vector<double> h_tmpl, h_yw, h_vr, h_kr;  // host copies (uploaded at create)
     // workspaces for the host-pointer entry points (capacity: max_scenarios * num_agents)
     double *w_states = nullptr, *w_targets = nullptr, *w_ctrl = nullptr, *w_obj = nullptr;
     int32_t *w_status = nullptr, *w_ncurves = nullptr, *w_iters = nullptr;
@@ -179,30 +179,6 @@ int build_device_tables(mpccbf_handle* h) {
             vr[i * K + k] = static_cast<double>(t.Vr(i, k));
             kr[i * K + k] = static_cast<double>(t.Kr(i, k));
         }
-    // ---- left inverse of W1 (recovers the whitened free dof from control points: slack verification) ----
-    {
-        std::vector<double>& gv = h->h_gv;
-        gv.assign(static_cast<size_t>(2) * t.m1 + 4, 0.0);
-        xreal a = 0, b = 0, c = 0;  // W1'W1 = [a b; b c]
-        for (int i = 0; i < t.m1; ++i) {
-            a += t.W1(i, 0) * t.W1(i, 0);
-            b += t.W1(i, 0) * t.W1(i, 1);
-            c += t.W1(i, 1) * t.W1(i, 1);
-        }
-        const xreal det = a * c - b * b;
-        xreal gy[2][2] = {{0, 0}, {0, 0}};
-        for (int i = 0; i < t.m1; ++i) {
-            const xreal g0 = (c * t.W1(i, 0) - b * t.W1(i, 1)) / det, g1 = (a * t.W1(i, 1) - b * t.W1(i, 0)) / det;
-            gv[i] = static_cast<double>(g0);
-            gv[t.m1 + i] = static_cast<double>(g1);
-            for (int j = 0; j < 2; ++j) {
-                gy[0][j] += g0 * t.Y1(i, j);
-                gy[1][j] += g1 * t.Y1(i, j);
-            }
-        }
-        for (int r = 0; r < 2; ++r)
-            for (int j = 0; j < 2; ++j) gv[2 * t.m1 + 2 * r + j] = static_cast<double>(gy[r][j]);
-    }
     // ---- polynomial structure of the bound rows along the horizon (see device_tables.h) ---------
     d.poly = 0;
     if (K >= 4) {
@@ -251,8 +227,6 @@ int build_device_tables(mpccbf_handle* h) {
         if ((rc = upload(yw, &h->d_yw)) != MPCCBF_OK) return rc;
         if ((rc = upload(vr, &h->d_vr)) != MPCCBF_OK) return rc;
         if ((rc = upload(kr, &h->d_kr)) != MPCCBF_OK) return rc;
-        if ((rc = upload(h->h_gv, &h->d_gv)) != MPCCBF_OK) return rc;
-        d.gv = h->d_gv;
         d.tmpl = h->d_tmpl;
         d.yw = h->d_yw;
         d.Vr = h->d_vr;
@@ -262,7 +236,6 @@ int build_device_tables(mpccbf_handle* h) {
         d.yw = yw.data();
         d.Vr = vr.data();
         d.Kr = kr.data();
-        d.gv = h->h_gv.data();
     }
     return MPCCBF_OK;
 }
@@ -292,7 +265,7 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
     if (slack_fast) {  // first tier: the hard-row optimum, kept wherever it is also the slack optimum
         const int rc = slack_prepare_hard(h->dev, a.num_qp, h->sw);
         if (rc != MPCCBF_OK) return rc;
-        if (!a.ctrl_all) a.ctrl_all = h->sw.hard_all;
+        a.v_all = h->sw.hard_all;
     }
     if (!h->slack_reduced || slack_fast) {
         int lanes = h->lanes;
@@ -326,7 +299,6 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
             rc = slack_verify(h->dev, h->cfg, a, h->sw, h->sm_count, stream, &nfb);
             if (rc != MPCCBF_OK) return rc;
             h->launches += 1;
-            if (a.ctrl_all == h->sw.hard_all) a.ctrl_all = nullptr;  // the caller did not ask for the iterates
             if (nfb > 0) rc = slack_step(h->dev, h->cfg, a, o, h->sw, h->sw.list, nfb, &h->launches);
         } else {
             rc = slack_step(h->dev, h->cfg, a, o, h->sw, nullptr, 0, &h->launches);
@@ -461,7 +433,7 @@ int mpccbf_destroy(mpccbf_handle* h) {
         for (void* q : eptrs)
             if (q) cudaFree(q);
         slack_free(h->sw);
-        void* ptrs[] = {h->d_tmpl, h->d_yw, h->d_vr, h->d_kr, h->d_gv, h->w_states, h->w_targets, h->w_ctrl, h->w_obj,
+        void* ptrs[] = {h->d_tmpl, h->d_yw, h->d_vr, h->d_kr, h->w_states, h->w_targets, h->w_ctrl, h->w_obj,
                         h->w_status, h->w_ncurves, h->w_iters, h->o_states, h->o_ref, h->o_ctrl, h->o_all, h->o_status};
         for (void* p : ptrs)
             if (p) cudaFree(p);

@@ -34,7 +34,6 @@ struct DevTables {
     const double* yw;    // [m1][4]  {Y1(.,0), Y1(.,1), W1(.,0), W1(.,1)}
     const double* Vr;    // [2][K]   general (per-step) reference
     const double* Kr;    // [2][K]
-    const double* gv;    // [2][m1] left inverse of W1, then [2][2] (that inverse times Y1): v = gv x_axis - gv_y [pos; vel]
 };
 
 }  // namespace mpccbf

@@ -456,6 +456,10 @@ __host__ __device__ void impc_agent(const DevTables& T, const StepArgs& a, int g
         ++n_ok;
 #pragma unroll
         for (int i = 0; i < R; ++i) vlast[i] = v[i];
+        if (a.v_all && gl == 0) {
+#pragma unroll
+            for (int i = 0; i < R; ++i) a.v_all[(static_cast<size_t>(g) * T.iters + it) * R + i] = v[i];
+        }
         if (a.ctrl_all) {
             double* out = a.ctrl_all + (static_cast<size_t>(g) * T.iters + it) * T.n;
             for (int i = gl; i < T.n; i += W) {

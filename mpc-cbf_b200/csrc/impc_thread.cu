@@ -496,6 +496,11 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         for (int i = 0; i < 4; ++i) vlast[i] = gx.v[i];
         vlast[4] = gy.v[0];
         vlast[5] = gy.v[1];
+        if (a.v_all) {  // slack-mode verification reads the iterates in whitened coordinates
+            double* vo = a.v_all + (sbase + it) * 6;
+#pragma unroll
+            for (int i = 0; i < 6; ++i) vo[i] = vlast[i];
+        }
         if (a.ctrl_all) {  // every iterate (mpccbf_optimize_one): small batches, direct stores
 #pragma unroll
             for (int ax = 0; ax < 3; ++ax) {

@@ -17,6 +17,7 @@ struct StepArgs {
     const double* targets;   // [B][3]  (ref_mode 0)  or  [B][3K] (ref_mode 1)
     double* ctrl_pts;        // [B][n]            last successful iterate (zeros if none)
     double* ctrl_all;        // [B][iters][n]     every successful iterate, may be NULL
+    double* v_all = nullptr; // [B][iters][6]     whitened free dof of every successful iterate, may be NULL
     int32_t* status;         // [B][iters]
     int32_t* n_curves;       // [B]   may be NULL
     double* objective;       // [B]   may be NULL
@@ -96,7 +97,7 @@ struct SlackWorkspace {
     int32_t *stat = nullptr, *it = nullptr, *nok = nullptr;
     // first tier (hard-row solve + verification): iterates of the fused kernels, agents for the ADMM tier
     size_t hard_cap = 0;
-    double* hard_all = nullptr;   // [hard_cap][iters][n]
+    double* hard_all = nullptr;   // [hard_cap][iters][6] whitened iterates of the hard-row solve
     int32_t* list = nullptr;      // [hard_cap]
     int32_t* count = nullptr;     // device counter
     int32_t* h_count = nullptr;   // pinned host copy
@@ -105,7 +106,7 @@ struct SlackWorkspace {
 int slack_step(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, const DenseOpts& o, SlackWorkspace& w,
                const int32_t* list, int count, int64_t* launches);
 // Buffers of the first tier for `num_qp` agents; then, after the fused hard-row kernels ran with
-// ctrl_all = a.ctrl_all, the verification: fills w.list and returns the number of agents in *n_fallback
+// v_all = w.hard_all, the verification: fills w.list and returns the number of agents in *n_fallback
 // (synchronises the stream).
 int slack_prepare_hard(const DevTables& T, int num_qp, SlackWorkspace& w);
 int slack_verify(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, SlackWorkspace& w, int sm_count,

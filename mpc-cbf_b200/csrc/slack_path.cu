@@ -303,7 +303,7 @@ __global__ void __launch_bounds__(kTA) slack_finish_kernel(const DevTables T, co
 // The slack QP min 1/2|v - v0|^2 + sum_j w_j s_j has the same minimiser as the hard-row QP (with s = 0) iff
 // the hard optimum's multipliers on neighbour j's safety rows sum to at most w_j (KKT of the slack QP with
 // mu_j = w_j - sum_k lambda_jk >= 0 on s_j >= 0). One warp per agent re-derives, per IMPC iterate of the
-// fused hard-row kernels, the active x/y rows at the returned point, solves the <= 4-column least-squares
+// fused hard-row kernels (their whitened iterates come through StepArgs::v_all), the active x/y rows, solves the <= 4-column least-squares
 // system v0 - v = sum_i lambda_i n_i, and accepts the agent when stationarity holds to 1e-7, lambda >= 0 and
 // every cap holds with margin. Everything else (infeasible hard QP, a cap exceeded, degenerate or more
 // than 4 active rows) goes to the ADMM tier through `list`.
@@ -313,7 +313,7 @@ struct SlackVerify {
     int ref_mode;
     int num_qp, agent_begin, agent_count;
     double slack_cost, slack_decay;
-    const double* ctrl_all;  // [B][iters][n] iterates of the hard-row solve
+    const double* v_all;     // [B][iters][6] iterates of the hard-row solve in whitened coordinates
     const int32_t* status;   // [B][iters]
     int32_t* list;
     int32_t* count;
@@ -323,7 +323,7 @@ constexpr int kVW = 4;  // warps per CTA
 __global__ void __launch_bounds__(kVW * 32) slack_verify_kernel(const DevTables T, const SlackVerify a) {
     extern __shared__ double vsm[];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const int N = T.N, K = T.K, J = N - 1, m1 = T.m1;
+    const int N = T.N, K = T.K, J = N - 1;
     double* st = vsm + static_cast<size_t>(wib) * (N * 6 + 24);
     double* nrm = st + N * 6;                      // [4][4] active normals
     int* nbi = reinterpret_cast<int*>(nrm + 16);   // [4] neighbour of a soft row, -1 for a bound row
@@ -344,14 +344,11 @@ __global__ void __launch_bounds__(kVW * 32) slack_verify_kernel(const DevTables 
                 pass = false;
                 break;
             }
-            // whitened free dof of this iterate from its control points, and v0 of the x / y axes
-            const double* x = a.ctrl_all + (static_cast<size_t>(g) * T.iters + it) * T.n;
+            // whitened free dof of this iterate and v0 of the x / y axes
             double mine = 0.0, mine0 = 0.0;
             if (lane < 6) {
                 const int ax = lane >> 1, r = lane & 1;
-                for (int i = 0; i < m1; ++i)
-                    mine = fma(T.gv[r * m1 + i], x[(i / T.c) * 3 * T.c + ax * T.c + (i % T.c)], mine);
-                mine -= T.gv[2 * m1 + 2 * r] * me[ax] + T.gv[2 * m1 + 2 * r + 1] * me[3 + ax];
+                mine = a.v_all[(static_cast<size_t>(g) * T.iters + it) * 6 + lane];
                 double rr = 0.0;
                 if (a.ref_mode == 0) {
                     rr = T.Vt[r] * __ldg(a.targets + static_cast<size_t>(g) * 3 + ax);
@@ -522,7 +519,7 @@ static void free_admm(SlackWorkspace& w) {  // the ADMM tier's buffers only (the
 
 int slack_prepare_hard(const DevTables& T, int num_qp, SlackWorkspace& w) {
     if (w.hard_cap >= static_cast<size_t>(num_qp)) return MPCCBF_OK;
-    bool ok = grow(&w.hard_all, static_cast<size_t>(num_qp) * T.iters * T.n) && grow(&w.list, static_cast<size_t>(num_qp));
+    bool ok = grow(&w.hard_all, static_cast<size_t>(num_qp) * T.iters * 6) && grow(&w.list, static_cast<size_t>(num_qp));
     if (!w.count) ok = ok && grow(&w.count, 1);
     if (!w.h_count) ok = ok && cudaMallocHost(reinterpret_cast<void**>(&w.h_count), sizeof(int32_t)) == cudaSuccess;
     if (!ok) {
@@ -539,7 +536,7 @@ int slack_verify(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a
     V.states = a.states; V.targets = a.targets; V.ref_mode = a.ref_mode;
     V.num_qp = a.num_qp; V.agent_begin = a.agent_begin; V.agent_count = a.agent_count;
     V.slack_cost = cfg.slack_cost; V.slack_decay = cfg.slack_decay;
-    V.ctrl_all = a.ctrl_all; V.status = a.status; V.list = w.list; V.count = w.count;
+    V.v_all = a.v_all; V.status = a.status; V.list = w.list; V.count = w.count;
     const size_t smem = sizeof(double) * kVW * (static_cast<size_t>(T.N) * 6 + 24);
     cudaError_t e = cudaMemsetAsync(w.count, 0, sizeof(int32_t), stream);
     if (e == cudaSuccess && smem > 48 * 1024)
