@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(kTA) slack_finish_kernel(const DevTables T, co
 // ---- first tier: is the hard-row optimum already the slack-mode optimum? --------------------------------
 // The slack QP min 1/2|v - v0|^2 + sum_j w_j s_j has the same minimiser as the hard-row QP (with s = 0) iff
 // the hard optimum's multipliers on neighbour j's safety rows sum to at most w_j (KKT of the slack QP with
-// mu_j = w_j - sum_k lambda_jk >= 0 on s_j >= 0). One warp per agent re-derives, per IMPC iterate of the
+// mu_j = w_j - sum_k lambda_jk >= 0 on s_j >= 0). One thread per agent re-derives, per IMPC iterate of the
 // fused hard-row kernels (their whitened iterates come through StepArgs::v_all), the active x/y rows, solves the <= 4-column least-squares
 // system v0 - v = sum_i lambda_i n_i, and accepts the agent when stationarity holds to 1e-7, lambda >= 0 and
 // every cap holds with margin. Everything else (infeasible hard QP, a cap exceeded, degenerate or more
@@ -318,25 +318,21 @@ struct SlackVerify {
     int32_t* list;
     int32_t* count;
 };
-constexpr int kVW = 4;  // warps per CTA
+constexpr int kVT = 128;  // threads per CTA, one agent each
 
-__global__ void __launch_bounds__(kVW * 32) slack_verify_kernel(const DevTables T, const SlackVerify a) {
-    extern __shared__ double vsm[];
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+__global__ void __launch_bounds__(kVT) slack_verify_kernel(const DevTables T, const SlackVerify a) {
+    extern __shared__ double tm[];  // [3][K][kTmplStride] row templates
     const int N = T.N, K = T.K, J = N - 1;
-    double* st = vsm + static_cast<size_t>(wib) * (N * 6 + 24);
-    double* nrm = st + N * 6;                      // [4][4] active normals
-    int* nbi = reinterpret_cast<int*>(nrm + 16);   // [4] neighbour of a soft row, -1 for a bound row
-    const double* tm = T.tmpl;
+    for (int i = threadIdx.x; i < 3 * K * kTmplStride; i += kVT) tm[i] = T.tmpl[i];
+    __syncthreads();
     const double tol = 1e-8;
-    const int nwarps = gridDim.x * kVW;
-    for (int g = blockIdx.x * kVW + wib; g < a.num_qp; g += nwarps) {
+    for (int g = blockIdx.x * kVT + threadIdx.x; g < a.num_qp; g += gridDim.x * kVT) {
         const int scen = g / a.agent_count;
         const int self = a.agent_begin + (g - scen * a.agent_count);
-        __syncwarp();
-        for (int i = lane; i < N * 6; i += 32) st[i] = __ldg(a.states + static_cast<size_t>(scen) * N * 6 + i);
-        __syncwarp();
-        const double* me = st + self * 6;
+        const double* st = a.states + static_cast<size_t>(scen) * N * 6;  // neighbours' states: L1/L2 hits
+        double me[6];
+#pragma unroll
+        for (int c = 0; c < 6; ++c) me[c] = __ldg(st + self * 6 + c);
         bool pass = true;
         double vprev[6] = {0, 0, 0, 0, 0, 0};
         for (int it = 0; it < T.iters && pass; ++it) {
@@ -344,11 +340,13 @@ __global__ void __launch_bounds__(kVW * 32) slack_verify_kernel(const DevTables 
                 pass = false;
                 break;
             }
-            // whitened free dof of this iterate and v0 of the x / y axes
-            double mine = 0.0, mine0 = 0.0;
-            if (lane < 6) {
-                const int ax = lane >> 1, r = lane & 1;
-                mine = a.v_all[(static_cast<size_t>(g) * T.iters + it) * 6 + lane];
+            // whitened free dof of this iterate, and v0 - v on the x / y axes
+            double v[6], r4[4];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) v[c] = a.v_all[(static_cast<size_t>(g) * T.iters + it) * 6 + c];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int ax = c >> 1, r = c & 1;
                 double rr = 0.0;
                 if (a.ref_mode == 0) {
                     rr = T.Vt[r] * __ldg(a.targets + static_cast<size_t>(g) * 3 + ax);
@@ -356,86 +354,75 @@ __global__ void __launch_bounds__(kVW * 32) slack_verify_kernel(const DevTables 
                     const double* rf = a.targets + static_cast<size_t>(g) * 3 * K;
                     for (int k = 0; k < K; ++k) rr = fma(T.Vr[r * K + k], __ldg(rf + 3 * k + ax), rr);
                 }
-                mine0 = T.Vs[r][0] * me[ax] + T.Vs[r][1] * me[3 + ax] + rr;
+                r4[c] = T.Vs[r][0] * me[ax] + T.Vs[r][1] * me[3 + ax] + rr - v[c];
             }
-            double v[6], r4[4];
-#pragma unroll
-            for (int c = 0; c < 6; ++c) v[c] = __shfl_sync(0xffffffffu, mine, c);
-#pragma unroll
-            for (int c = 0; c < 4; ++c) r4[c] = __shfl_sync(0xffffffffu, mine0, c) - v[c];
             // ---- active x / y rows at v ------------------------------------------------------------------
-            const int hit = it == 0 ? 1 : T.H;
-            const int total = 4 * K + J * hit;
+            double nrm[4][4];
+            int nbi[4] = {-1, -1, -1, -1};
             int cnt = 0;
-            for (int base = 0; base < total; base += 32) {
-                const int e = base + lane;
-                bool active = false;
-                double n4[4] = {0, 0, 0, 0};
-                int nb = -1;
-                if (e < 4 * K) {
-                    const int dsel = e >= 2 * K ? 1 : 0;
-                    const int rr = e - dsel * 2 * K;
-                    const int k = rr >> 1, ax = rr & 1;
-                    const double* tk = tm + ((2 - dsel) * K + k) * kTmplStride;
-                    if (tk[0] != 0.0 || tk[1] != 0.0) {
-                        const double val = tk[0] * v[2 * ax] + tk[1] * v[2 * ax + 1] + tk[2] * me[ax] + tk[3] * me[3 + ax];
-                        const double lo = T.lim_lo[dsel][ax], hi = T.lim_hi[dsel][ax];
-                        double sgn = 0.0;
-                        if (hi < 1e20 && fabs(val - hi) <= tol * (1.0 + fabs(hi))) sgn = 1.0;
-                        else if (lo > -1e20 && fabs(val - lo) <= tol * (1.0 + fabs(lo))) sgn = -1.0;
-                        if (sgn != 0.0) {
-                            active = true;
-                            n4[2 * ax] = sgn * tk[0];
-                            n4[2 * ax + 1] = sgn * tk[1];
-                        }
+            for (int e = 0; e < 4 * K; ++e) {  // bound rows: acceleration block, then velocity block
+                const int dsel = e >= 2 * K ? 1 : 0;
+                const int rr = e - dsel * 2 * K;
+                const int k = rr >> 1, ax = rr & 1;
+                const double* tk = tm + ((2 - dsel) * K + k) * kTmplStride;
+                if (tk[0] == 0.0 && tk[1] == 0.0) continue;
+                const double val = tk[0] * (ax ? v[2] : v[0]) + tk[1] * (ax ? v[3] : v[1]) + tk[2] * me[ax] + tk[3] * me[3 + ax];
+                const double lo = T.lim_lo[dsel][ax], hi = T.lim_hi[dsel][ax];
+                double sgn = 0.0;
+                if (hi < 1e20 && fabs(val - hi) <= tol * (1.0 + fabs(hi))) sgn = 1.0;
+                else if (lo > -1e20 && fabs(val - lo) <= tol * (1.0 + fabs(lo))) sgn = -1.0;
+                if (sgn != 0.0) {
+                    if (cnt < 4) {
+                        nrm[cnt][0] = ax ? 0.0 : sgn * tk[0];
+                        nrm[cnt][1] = ax ? 0.0 : sgn * tk[1];
+                        nrm[cnt][2] = ax ? sgn * tk[0] : 0.0;
+                        nrm[cnt][3] = ax ? sgn * tk[1] : 0.0;
+                        nbi[cnt] = -1;
                     }
-                } else if (e < total) {
-                    const int r = e - 4 * K;
-                    nb = r / hit;
-                    const int k = r - nb * hit;
-                    const int other = nb + (nb >= self ? 1 : 0);
-                    double px = me[0], py = me[1], vx = me[3], vy = me[4];
-                    if (it > 0) {  // predicted ego state at t_k from the previous iterate
-                        const double* t0 = tm + (0 * K + k) * kTmplStride;
-                        const double* t1 = tm + (1 * K + k) * kTmplStride;
-                        px = t0[0] * vprev[0] + t0[1] * vprev[1] + t0[2] * me[0] + t0[3] * me[3];
-                        py = t0[0] * vprev[2] + t0[1] * vprev[3] + t0[2] * me[1] + t0[3] * me[4];
-                        vx = t1[0] * vprev[0] + t1[1] * vprev[1] + t1[2] * me[0] + t1[3] * me[3];
-                        vy = t1[0] * vprev[2] + t1[1] * vprev[3] + t1[2] * me[1] + t1[3] * me[4];
-                    }
-                    const double* o = st + other * 6;
-                    double ax, ay, bb;
-                    safety_hocbf(px, py, vx, vy, o[0], o[1], o[3], o[4], T.dmin2, T.gamma, ax, ay, bb);
-                    const double* tk = tm + (2 * K + k) * kTmplStride;
-                    n4[0] = -ax * tk[0];
-                    n4[1] = -ax * tk[1];
-                    n4[2] = -ay * tk[0];
-                    n4[3] = -ay * tk[1];
-                    const double ub = bb + ax * (tk[2] * me[0] + tk[3] * me[3]) + ay * (tk[2] * me[1] + tk[3] * me[4]);
-                    const double val = n4[0] * v[0] + n4[1] * v[1] + n4[2] * v[2] + n4[3] * v[3];
-                    active = fabs(val - ub) <= tol * (1.0 + fabs(ub));
+                    ++cnt;
                 }
-                const unsigned bal = __ballot_sync(0xffffffffu, active);
-                const int slot = cnt + __popc(bal & ((1u << lane) - 1u));
-                if (active && slot < 4) {
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) nrm[slot * 4 + c] = n4[c];
-                    nbi[slot] = nb;
-                }
-                cnt += __popc(bal);
             }
-            __syncwarp();
+            const int hit = it == 0 ? 1 : T.H;
+            for (int k = 0; k < hit; ++k) {  // safety rows of horizon step k
+                double px = me[0], py = me[1], vx = me[3], vy = me[4];
+                if (it > 0) {  // predicted ego state at t_k from the previous iterate
+                    const double* t0 = tm + (0 * K + k) * kTmplStride;
+                    const double* t1 = tm + (1 * K + k) * kTmplStride;
+                    px = t0[0] * vprev[0] + t0[1] * vprev[1] + t0[2] * me[0] + t0[3] * me[3];
+                    py = t0[0] * vprev[2] + t0[1] * vprev[3] + t0[2] * me[1] + t0[3] * me[4];
+                    vx = t1[0] * vprev[0] + t1[1] * vprev[1] + t1[2] * me[0] + t1[3] * me[3];
+                    vy = t1[0] * vprev[2] + t1[1] * vprev[3] + t1[2] * me[1] + t1[3] * me[4];
+                }
+                const double* tk = tm + (2 * K + k) * kTmplStride;
+                const double ux = tk[0] * v[0] + tk[1] * v[1] + tk[2] * me[0] + tk[3] * me[3];  // acceleration at t_k
+                const double uy = tk[0] * v[2] + tk[1] * v[3] + tk[2] * me[1] + tk[3] * me[4];
+                for (int nb = 0; nb < J; ++nb) {
+                    const double* o = st + (nb + (nb >= self ? 1 : 0)) * 6;
+                    double ax, ay, bb;
+                    safety_hocbf(px, py, vx, vy, __ldg(o), __ldg(o + 1), __ldg(o + 3), __ldg(o + 4), T.dmin2, T.gamma, ax, ay, bb);
+                    const double slack = ax * ux + ay * uy + bb;  // row: a.u + b >= 0
+                    if (fabs(slack) <= tol * (1.0 + fabs(bb))) {
+                        if (cnt < 4) {
+                            nrm[cnt][0] = -ax * tk[0];
+                            nrm[cnt][1] = -ax * tk[1];
+                            nrm[cnt][2] = -ay * tk[0];
+                            nrm[cnt][3] = -ay * tk[1];
+                            nbi[cnt] = nb;
+                        }
+                        ++cnt;
+                    }
+                }
+            }
             if (cnt > 4) {
                 pass = false;
                 break;
             }
-            // ---- multipliers: least squares on the active normals (every lane, same arithmetic) ----------
+            // ---- multipliers: least squares on the active normals ----------------------------------------
             double G[4][4], rhs[4], lam[4] = {0, 0, 0, 0};
             for (int i = 0; i < cnt; ++i) {
-                rhs[i] = nrm[i * 4] * r4[0] + nrm[i * 4 + 1] * r4[1] + nrm[i * 4 + 2] * r4[2] + nrm[i * 4 + 3] * r4[3];
+                rhs[i] = nrm[i][0] * r4[0] + nrm[i][1] * r4[1] + nrm[i][2] * r4[2] + nrm[i][3] * r4[3];
                 for (int j = 0; j <= i; ++j)
-                    G[i][j] = nrm[i * 4] * nrm[j * 4] + nrm[i * 4 + 1] * nrm[j * 4 + 1] + nrm[i * 4 + 2] * nrm[j * 4 + 2] +
-                              nrm[i * 4 + 3] * nrm[j * 4 + 3];
+                    G[i][j] = nrm[i][0] * nrm[j][0] + nrm[i][1] * nrm[j][1] + nrm[i][2] * nrm[j][2] + nrm[i][3] * nrm[j][3];
             }
             for (int j = 0; j < cnt && pass; ++j) {  // Cholesky G = L L'
                 double d = G[j][j];
@@ -466,7 +453,7 @@ __global__ void __launch_bounds__(kVW * 32) slack_verify_kernel(const DevTables 
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 double e = r4[c];
-                for (int i = 0; i < cnt; ++i) e -= lam[i] * nrm[i * 4 + c];
+                for (int i = 0; i < cnt; ++i) e -= lam[i] * nrm[i][c];
                 res = fmax(res, fabs(e));
                 rmax = fmax(rmax, fabs(r4[c]));
             }
@@ -487,9 +474,8 @@ __global__ void __launch_bounds__(kVW * 32) slack_verify_kernel(const DevTables 
             }
 #pragma unroll
             for (int c = 0; c < 6; ++c) vprev[c] = v[c];
-            __syncwarp();
         }
-        if (!pass && lane == 0) a.list[atomicAdd(a.count, 1)] = g;
+        if (!pass) a.list[atomicAdd(a.count, 1)] = g;
     }
 }
 
@@ -537,13 +523,11 @@ int slack_verify(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a
     V.num_qp = a.num_qp; V.agent_begin = a.agent_begin; V.agent_count = a.agent_count;
     V.slack_cost = cfg.slack_cost; V.slack_decay = cfg.slack_decay;
     V.v_all = a.v_all; V.status = a.status; V.list = w.list; V.count = w.count;
-    const size_t smem = sizeof(double) * kVW * (static_cast<size_t>(T.N) * 6 + 24);
+    const size_t smem = sizeof(double) * 3 * T.K * kTmplStride;
     cudaError_t e = cudaMemsetAsync(w.count, 0, sizeof(int32_t), stream);
-    if (e == cudaSuccess && smem > 48 * 1024)
-        e = cudaFuncSetAttribute(slack_verify_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e == cudaSuccess) {
-        const int grid = std::min((a.num_qp + kVW - 1) / kVW, 16 * std::max(1, sm_count));
-        slack_verify_kernel<<<grid, kVW * 32, smem, stream>>>(T, V);
+        const int grid = std::min((a.num_qp + kVT - 1) / kVT, 8 * std::max(1, sm_count));
+        slack_verify_kernel<<<grid, kVT, smem, stream>>>(T, V);
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaMemcpyAsync(w.h_count, w.count, sizeof(int32_t), cudaMemcpyDeviceToHost, stream);
