@@ -64,13 +64,15 @@ __device__ __forceinline__ void safety_hocbf(double px, double py, double vx, do
 __device__ double slack_weight(const double* st, int self, int j, int J, double cost, double decay) {
     const double* me = st + self * 6;
     const int other = j + (j >= self ? 1 : 0);
+    // near-ties decide ranks in symmetric formations: the same double arithmetic as the host code of the
+    // reference (separately rounded products and sum, no fma), exact ties by index
     const double dx = st[other * 6] - me[0], dy = st[other * 6 + 1] - me[1];
-    const double dj = sqrt(dx * dx + dy * dy);
+    const double dj = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
     int rank = 0;
     for (int i = 0; i < J; ++i) {
         const int oi = i + (i >= self ? 1 : 0);
         const double ex = st[oi * 6] - me[0], ey = st[oi * 6 + 1] - me[1];
-        const double di = sqrt(ex * ex + ey * ey);
+        const double di = sqrt(__dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey)));
         rank += (di < dj || (di == dj && i < j)) ? 1 : 0;
     }
     return cost * pow(decay, static_cast<double>(rank));

@@ -281,10 +281,15 @@ struct Controller {
             int j = 0;
             for (int o = 0; o < N; ++o) {
                 if (o == self) continue;
-                const R ddx = states[6 * o] - x0[0], ddy = states[6 * o + 1] - x0[1];
-                dist[j++] = std::sqrt(ddx * ddx + ddy * ddy);
+                // the reference computes these distances in double (std::vector<T>, T = double) whatever the
+                // precision of this oracle run, and near-ties (symmetric formations) decide the ranks: plain
+                // double products and sum, no contraction into an fma
+                const double ddx = static_cast<double>(states[6 * o]) - static_cast<double>(x0[0]);
+                const double ddy = static_cast<double>(states[6 * o + 1]) - static_cast<double>(x0[1]);
+                volatile double xx = ddx * ddx, yy = ddy * ddy;
+                dist[j++] = R(std::sqrt(xx + yy));
             }
-            std::sort(idx.begin(), idx.end(), [&](size_t a, size_t b) { return dist[a] < dist[b]; });
+            std::stable_sort(idx.begin(), idx.end(), [&](size_t a, size_t b) { return dist[a] < dist[b]; });  // exact ties: index order
             for (int i = 0; i < nn; ++i)
                 slack_w[idx[i]] = R(cfg.slack_cost) * std::pow(R(cfg.slack_decay), R(i));
         }
