@@ -108,31 +108,30 @@ def main():
           "note": "host-pointer entry: the time includes H2D of P, A (42 MB) and D2H; see the ncu duration for the kernel alone"})
     h.close()
 
-    # ---- slack-mode controller step (slack_path.cu: assemble -> dense ADMM -> finish per IMPC iteration) ----------
+    # ---- slack-mode controller step (capped multipliers inside the fused thread-per-agent kernel) ----------------
     import bench
     from parity import dense_scenarios
     N = 16
-    for label, S, maker in (("ring swarms of bench.py", 1024, lambda S: bench.make_swarm(S, N, 7)),
-                            ("packed grids near d_min (half infeasible without slack)", 256,
+    for label, S, maker in (("ring swarms of bench.py", 4096, lambda S: bench.make_swarm(S, N, 7)),
+                            ("packed grids near d_min (half infeasible without slack)", 4096,
                              lambda S: dense_scenarios(S, N, N, 0.8, spread=1.15, vmax=1.0))):
-        cfg = M.default_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N, max_scenarios=S, slack_mode=1,
-                               slack_cost=50000.0, slack_decay=0.1)
-        h = M.Handle(cfg)
         stn, tgn = maker(S)
         d_st, d_tg = torch.tensor(stn, device="cuda"), torch.tensor(tgn, device="cuda")
-        cp = torch.zeros((S, N, h.n), dtype=torch.float64, device="cuda")
-        stat = torch.zeros((S, N, 2), dtype=torch.int32, device="cuda")
-        f0 = h.slack_fallback_count()
-        ms = timed(lambda: h.step_batch(S, d_st, d_tg, cp, stat), 3, torch)
-        fallback = (h.slack_fallback_count() - f0) // 6  # 3 warm-up + 3 timed calls
-        its = h.last_iteration_counts(S * N * 2)
-        sc = np.bincount(stat.cpu().numpy().ravel(), minlength=8)
-        emit({"kernel": "slack-mode controller step (fused hard-row kernel + slack_verify; ADMM tier = slack_assemble + dense_qp + slack_finish x2 for the agents that need slack)",
-              "agents_through_admm_tier": int(fallback), "agents": S * N,
-              "shape": f"{S} x {N} agents, {label}; QPs of {6 + N - 1} variables, {15 + 120 + 15} / {30 + 120 + 15} rows",
-              "ms": ms, "qps_per_s": S * N * 2 / (ms * 1e-3), "iterations_p50_p90_p99 (active-set steps on tier 1, ADMM on tier 2)": [float(v) for v in np.percentile(its, [50, 90, 99])],
-              "status_counts": {str(i): int(v) for i, v in enumerate(sc) if v}})
-        h.close()
+        for slack in (1, 0):
+            cfg = M.default_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N, max_scenarios=S, slack_mode=slack,
+                                   slack_cost=50000.0, slack_decay=0.1)
+            h = M.Handle(cfg)
+            cp = torch.zeros((S, N, h.n), dtype=torch.float64, device="cuda")
+            stat = torch.zeros((S, N, 2), dtype=torch.int32, device="cuda")
+            ms = timed(lambda: h.step_batch(S, d_st, d_tg, cp, stat), 5, torch)
+            its = h.last_iteration_counts(S * N * 2)
+            sc = np.bincount(stat.cpu().numpy().ravel(), minlength=8)
+            emit({"kernel": "impc_thread_kernel<SOFT=%d> controller step, slack_mode = %d" % (slack, slack), "agents": S * N,
+                  "shape": f"{S} x {N} agents, {label}",
+                  "ms": ms, "qps_per_s": S * N * 2 / (ms * 1e-3),
+                  "active_set_steps_p50_p90_p99": [float(v) for v in np.percentile(its, [50, 90, 99])],
+                  "status_counts": {str(i): int(v) for i, v in enumerate(sc) if v}})
+            h.close()
 
     if a.out:
         with open(a.out, "w") as f:

@@ -348,7 +348,7 @@ class Handle:
                                                   _ptr(n_curves), _ptr(next_states), stream))
 
     def slack_fallback_count(self):
-        """Agent-steps of this handle that needed the slack variables (second tier), cumulative."""
+        """Always 0 since round 2 (the slack caps live in the active-set kernel; kept for round-1 callers)."""
         return int(self._L.mpccbf_slack_fallback_count(self._h))
 
     def last_iteration_counts_ptr(self):

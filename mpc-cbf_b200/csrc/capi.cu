@@ -45,11 +45,9 @@ struct mpccbf_handle {
     double *e_curve = nullptr, *e_evalt = nullptr, *e_mind2 = nullptr, *e_ctrl = nullptr, *e_sub = nullptr, *e_tg = nullptr;
     int32_t *e_has = nullptr, *e_done = nullptr, *e_finish = nullptr, *e_failed = nullptr, *e_status = nullptr, *e_nc = nullptr;
     unsigned char* e_reached = nullptr;
-    // slack-mode controller path: reduced (6 + N-1)-variable QPs through the dense kernel (slack_path.cu)
-    bool slack_reduced = false;
-    bool slack_fast = true;        // try the hard-row kernels first and verify (MPCCBF_SLACK_FAST=0: ADMM for all)
-    int64_t slack_fallbacks = 0;   // agent-steps that went to the ADMM tier
-    SlackWorkspace sw;
+    // slack mode (cbf_params.slack_mode): capped multipliers inside the fused thread-per-agent kernel
+    // (gi_solver.h); scratch = one leader byte per (agent, neighbour)
+    unsigned char* w_lead = nullptr;
     int64_t launches = 0, qps = 0;
 };
 
@@ -104,6 +102,9 @@ int build_device_tables(mpccbf_handle* h) {
     d.dmin2 = h->cfg.d_min * h->cfg.d_min;
     d.gamma = h->cfg.cbf_gamma;
     d.feas_tol = h->cfg.feas_tol > 0 ? h->cfg.feas_tol : 1e-9;
+    d.slack = h->cfg.slack_mode ? 1 : 0;
+    d.slack_cost = h->cfg.slack_cost;
+    d.slack_decay = h->cfg.slack_decay;
     // rollout constants: t = h with the reference's lower_bound piece rule
     {
         RolloutConst& rc = h->rc;
@@ -243,7 +244,7 @@ int build_device_tables(mpccbf_handle* h) {
 int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_count, const double* states,
              const double* targets, int ref_mode, double* ctrl, double* ctrl_all, int32_t* status,
              int32_t* n_curves, double* objective, int32_t* iters, cudaStream_t stream) {
-    if (h->solver != MPCCBF_SOLVER_REDUCED && !h->slack_reduced) {
+    if (h->solver != MPCCBF_SOLVER_REDUCED) {
         set_error("controller path: this configuration does not reduce to the 6-dof form (needs cubic pieces with "
                   "C^3 continuity); use mpccbf_solve_qp_dense for the assembled QP");
         return MPCCBF_ERR_UNSUPPORTED;
@@ -261,51 +262,24 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
     a.agent_begin = agent_begin;
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
-    const bool slack_fast = h->slack_reduced && h->slack_fast;
-    if (slack_fast) {  // first tier: the hard-row optimum, kept wherever it is also the slack optimum
-        const int rc = slack_prepare_hard(h->dev, a.num_qp, h->sw);
-        if (rc != MPCCBF_OK) return rc;
-        a.v_all = h->sw.hard_all;
+    a.lead_ws = h->w_lead;
+    int lanes = h->lanes;
+    if (lanes < 0) {
+        // Measured crossover on B200 (profiles/r1h_kernel_crossover.md): a warp per agent (32 lanes split
+        // the row scan) wins while all its warps fit in one wave of 8 per SM — twice that for dense swarms,
+        // where a scan walks hundreds of safety rows; the thread-per-agent kernel wins beyond. The 8-lane
+        // variant is only the large-batch fallback for configurations without the polynomial row structure.
+        const int wave = 8 * h->sm_count * (h->cfg.num_agents >= 128 ? 2 : 1);
+        lanes = (a.num_qp <= wave) ? 32 : 0;
     }
-    if (!h->slack_reduced || slack_fast) {
-        int lanes = h->lanes;
-        if (lanes < 0) {
-            // Measured crossover on B200 (profiles/r1h_kernel_crossover.md): a warp per agent (32 lanes split
-            // the row scan) wins while all its warps fit in one wave of 8 per SM — twice that for dense swarms,
-            // where a scan walks hundreds of safety rows; the thread-per-agent kernel wins beyond. The 8-lane
-            // variant is only the large-batch fallback for configurations without the polynomial row structure.
-            const int wave = 8 * h->sm_count * (h->cfg.num_agents >= 128 ? 2 : 1);
-            lanes = (a.num_qp <= wave) ? 32 : 0;
-        }
-        if (lanes == 0 && !h->dev.poly)  // the thread kernel needs the polynomial row structure
-            lanes = (a.num_qp >= 2048 && h->cfg.num_agents < 64) ? 8 : 32;
-        if (lanes == 0)
-            CUDA_TRY(launch_impc_thread(h->dev, a, h->sm_count, stream));
-        else
-            CUDA_TRY(launch_impc_reduced(h->dev, a, lanes, h->sm_count, stream));
-        h->launches += 1;
-    }
-    if (h->slack_reduced) {
-        DenseOpts o;
-        o.max_iter = h->cfg.admm_max_iter;
-        o.check_every = h->cfg.admm_check_every;
-        o.eps = h->cfg.admm_eps;
-        o.rho = h->cfg.admm_rho;
-        o.sigma = h->cfg.admm_sigma;
-        o.sm_count = h->sm_count;
-        o.stream = stream;
-        int rc = MPCCBF_OK, nfb = a.num_qp;
-        if (slack_fast) {
-            rc = slack_verify(h->dev, h->cfg, a, h->sw, h->sm_count, stream, &nfb);
-            if (rc != MPCCBF_OK) return rc;
-            h->launches += 1;
-            if (nfb > 0) rc = slack_step(h->dev, h->cfg, a, o, h->sw, h->sw.list, nfb, &h->launches);
-        } else {
-            rc = slack_step(h->dev, h->cfg, a, o, h->sw, nullptr, 0, &h->launches);
-        }
-        if (rc != MPCCBF_OK) return rc;
-        h->slack_fallbacks += nfb;
-    }
+    if (h->cfg.slack_mode) lanes = 0;  // capped multipliers live in the thread-per-agent kernel only
+    if (lanes == 0 && !h->dev.poly)  // the thread kernel needs the polynomial row structure
+        lanes = (a.num_qp >= 2048 && h->cfg.num_agents < 64) ? 8 : 32;
+    if (lanes == 0)
+        CUDA_TRY(launch_impc_thread(h->dev, a, h->sm_count, stream));
+    else
+        CUDA_TRY(launch_impc_reduced(h->dev, a, lanes, h->sm_count, stream));
+    h->launches += 1;
     h->qps += static_cast<int64_t>(a.num_qp) * h->cfg.impc_iter;
     return MPCCBF_OK;
 }
@@ -347,21 +321,17 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
         delete h;
         return MPCCBF_ERR_INVALID;
     }
-    const bool can_reduce = h->tab.reducible && h->tab.r1 == 2 && !h->cfg.slack_mode && h->cfg.num_agents >= 1;
+    const bool can_reduce = h->tab.reducible && h->tab.r1 == 2 && h->cfg.num_agents >= 1;
     if (cfg->solver == MPCCBF_SOLVER_REDUCED && !can_reduce) {
         set_error("MPCCBF_SOLVER_REDUCED requested but the configuration does not reduce to the 6-dof form");
         delete h;
         return MPCCBF_ERR_UNSUPPORTED;
     }
     h->solver = (cfg->solver == MPCCBF_SOLVER_DENSE || !can_reduce) ? MPCCBF_SOLVER_DENSE : MPCCBF_SOLVER_REDUCED;
-    // slack mode keeps the null-space reduction of the equality rows but not the strictly convex solver
-    h->slack_reduced = h->cfg.slack_mode && h->tab.reducible && h->tab.r1 == 2 && h->cfg.num_agents >= 1 &&
-                       cfg->solver != MPCCBF_SOLVER_REDUCED;
     if (const char* env = std::getenv("MPCCBF_LANES")) {
         const int w = std::atoi(env);
         if (w == 32 || w == 8 || w == 1 || w == 0) h->lanes = w;
     }
-    if (const char* env = std::getenv("MPCCBF_SLACK_FAST")) h->slack_fast = std::atoi(env) != 0;
     h->device = cfg->device;
     if (cfg->device >= 0) {
         int count = 0;
@@ -389,7 +359,7 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
         if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
             cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking) != cudaSuccess) {
             set_error("cudaStreamCreate failed");
-            delete h;
+            mpccbf_destroy(h);
             return MPCCBF_ERR_CUDA;
         }
     }
@@ -397,6 +367,12 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
     if (rc != MPCCBF_OK) {
         mpccbf_destroy(h);
         return rc;
+    }
+    if (h->cfg.slack_mode && h->solver == MPCCBF_SOLVER_REDUCED && !h->dev.poly) {
+        set_error("slack mode needs the polynomial row structure of the thread-per-agent kernel (k_hor in 4..127, finite "
+                  "velocity and acceleration limits)");
+        mpccbf_destroy(h);
+        return MPCCBF_ERR_UNSUPPORTED;
     }
     if (h->has_device) {
         const size_t B = static_cast<size_t>(cfg->max_scenarios) * cfg->num_agents;
@@ -414,6 +390,7 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
         ok &= cudaMalloc(&h->o_ctrl, sizeof(double) * n) == cudaSuccess;
         ok &= cudaMalloc(&h->o_all, sizeof(double) * n * it) == cudaSuccess;
         ok &= cudaMalloc(&h->o_status, sizeof(int32_t) * (it + 1 + it)) == cudaSuccess;
+        if (h->cfg.slack_mode) ok &= cudaMalloc(&h->w_lead, std::max<size_t>(B * (N > 1 ? N - 1 : 1), 1)) == cudaSuccess;
         if (!ok) {
             set_error("device workspace allocation failed");
             mpccbf_destroy(h);
@@ -432,7 +409,7 @@ int mpccbf_destroy(mpccbf_handle* h) {
                          h->e_done, h->e_finish, h->e_failed};
         for (void* q : eptrs)
             if (q) cudaFree(q);
-        slack_free(h->sw);
+        if (h->w_lead) cudaFree(h->w_lead);
         void* ptrs[] = {h->d_tmpl, h->d_yw, h->d_vr, h->d_kr, h->w_states, h->w_targets, h->w_ctrl, h->w_obj,
                         h->w_status, h->w_ncurves, h->w_iters, h->o_states, h->o_ref, h->o_ctrl, h->o_all, h->o_status};
         for (void* p : ptrs)
@@ -891,7 +868,9 @@ int mpccbf_linear_cost(const mpccbf_handle* h, const double* x0, const double* r
     return MPCCBF_OK;
 }
 
-int64_t mpccbf_slack_fallback_count(const mpccbf_handle* h) { return h ? h->slack_fallbacks : -1; }
+// Round 1 had a second (ADMM) tier for slack-mode QPs; the caps now live in the active-set kernel and
+// nothing falls back. Kept so that callers built against the round-1 header keep linking.
+int64_t mpccbf_slack_fallback_count(const mpccbf_handle* h) { return h ? 0 : -1; }
 
 int mpccbf_get_counters(const mpccbf_handle* h, int64_t* kernel_launches, int64_t* qps_solved) {
     if (!h) return MPCCBF_ERR_INVALID;

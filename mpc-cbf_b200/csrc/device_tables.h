@@ -19,6 +19,8 @@ struct DevTables {
     double dmin2;       // d_min^2
     double gamma;       // class-K gain (5.0)
     double feas_tol;
+    int32_t slack;      // slack mode: safety rows of one neighbour share a slack of weight slack_cost * slack_decay^rank
+    double slack_cost, slack_decay;
     double Vs[2][2];    // v0 = Vs [pos;vel] + Vt target      (per axis)
     double Vt[2];
     double Kc[2][2];    // c0 = s'Kc s + target (Kt.s)        (per axis)

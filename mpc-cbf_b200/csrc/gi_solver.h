@@ -4,7 +4,25 @@
 // Used by the thread-per-agent fused kernel with D = 4 (x/y axes, coupled by the CBF rows) and
 // D = 2 (yaw axis, decoupled). The state is resumable: gi_run can be called again after more rows
 // became visible to the row provider (the iterate of a sub-problem is a valid dual-feasible
-// starting point for the larger problem).
+// starting point for the larger problem), and it can be rebuilt from the ids and multipliers of
+// its active rows alone (gi_rebuild), which is how the stage-A solution of an agent is restored
+// before a later IMPC iteration without keeping a copy of J and R.
+//
+// SOFT rows (slack mode, ConnectivityIMPCCBF.cpp:76-100 + MPCCBFQPGeneratorBase.cpp:28-38,80-135):
+// the safety rows of neighbour j share one slack variable s_j >= 0 with linear cost w_j. With the
+// slacks eliminated the QP is
+//      min 1/2 |v - v0|^2 + sum_j w_j max(0, max_k g_jk(v)),   g_jk(v) = rhs_jk - n_jk . v,
+// whose optimality conditions are those of the hard-row QP with the multipliers of one group
+// capped: lambda_jk >= 0, sum_k lambda_jk <= w_j. The group's pieces are its rows plus the zero
+// function ("none"); one piece is the group's LEADER (the one attaining the max; "none" while the
+// slack is zero) and carries the weight that is not on the other pieces. Every other piece k is
+// the generalised row  (n_k - n_lead) . v >= rhs_k - rhs_lead. The dual active-set iteration is
+// the usual one with a third step-length rule: the step stops where a group's multiplier sum
+// reaches its weight; there the leadership passes to an active row of that group (which leaves
+// the active set: its multiplier is now implicit), or to the entering row itself when the group
+// has no active row — the row is then "absorbed" by its slack and the major iteration ends.
+// The reverse face (a slack returning to zero) is the piece "none" of a group whose leader is a
+// row. This removes the separate slack-variable QP: same minimiser v, s_j = max(0, g_lead(v)).
 //
 // Replaces qpcpp::CPLEXSolver::solve (qpcpp/src/solvers/CPLEX.cpp:35-178) for the reduced QP.
 #pragma once
@@ -24,11 +42,19 @@ struct GIState {
     double Rm[D][D];  // upper triangular, leading q x q block used
     double u[D];      // multipliers of the active rows
     double v[D];      // current iterate
+    int id[D];        // row id of each active column
     int q;            // number of active rows
 };
 
+// group bookkeeping of the active columns (SOFT rows only)
 template <int D>
-MPCCBF_HD void gi_init(GIState<D>& g, const double* v0) {
+struct GISoft {
+    int grp[D];      // group of each active column (-1: hard row)
+    double cap[D];   // weight of that group
+};
+
+template <int D>
+MPCCBF_HD void gi_reset_factor(GIState<D>& g) {
 #pragma unroll
     for (int i = 0; i < D; ++i) {
 #pragma unroll
@@ -36,19 +62,132 @@ MPCCBF_HD void gi_init(GIState<D>& g, const double* v0) {
             g.J[i][j] = (i == j) ? 1.0 : 0.0;
             g.Rm[i][j] = 0.0;
         }
+    }
+}
+
+template <int D>
+MPCCBF_HD void gi_init(GIState<D>& g, const double* v0) {
+    gi_reset_factor<D>(g);
+#pragma unroll
+    for (int i = 0; i < D; ++i) {
         g.u[i] = 0.0;
         g.v[i] = v0[i];
+        g.id[i] = -1;
     }
     g.q = 0;
+}
+
+// d = J' n
+template <int D>
+MPCCBF_HD void gi_project(const GIState<D>& g, const double (&np)[D], double (&d)[D]) {
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+        double s = 0.0;
+#pragma unroll
+        for (int i = 0; i < D; ++i) s = fma(g.J[i][j], np[i], s);
+        d[j] = s;
+    }
+}
+
+// Appends the column whose projection is d = J' n: rotates d[q..] onto e_q (Givens from the bottom,
+// carried into J2) and stores R's new column. The caller sets u / id of the new column.
+template <int D>
+MPCCBF_HD void gi_add_column(GIState<D>& g, double (&d)[D]) {
+#pragma unroll
+    for (int k = D - 1; k >= 1; --k) {
+        if (k > g.q) {
+            const double a = d[k - 1], b = d[k];
+            const double hh = sqrt(fma(a, a, b * b));
+            if (hh > 0.0) {
+                const double ih = 1.0 / hh;
+                const double cs = a * ih, sn = b * ih;
+                d[k - 1] = hh;
+                d[k] = 0.0;
+#pragma unroll
+                for (int i = 0; i < D; ++i) {
+                    const double a1 = g.J[i][k - 1], a2 = g.J[i][k];
+                    g.J[i][k - 1] = fma(cs, a1, sn * a2);
+                    g.J[i][k] = fma(-sn, a1, cs * a2);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int col = 0; col < D; ++col)
+        if (col == g.q) {
+#pragma unroll
+            for (int i = 0; i <= col; ++i) g.Rm[i][col] = d[i];
+        }
+    ++g.q;
+}
+
+// Removes active column lpos (R becomes upper Hessenberg from there; Givens restore the triangle).
+template <int D>
+MPCCBF_HD void gi_drop_column(GIState<D>& g, int lpos) {
+#pragma unroll
+    for (int col = 0; col < D - 1; ++col)
+        if (col >= lpos) {
+#pragma unroll
+            for (int i = 0; i <= col + 1; ++i) g.Rm[i][col] = g.Rm[i][col + 1];  // Hessenberg part
+            g.u[col] = g.u[col + 1];
+            g.id[col] = g.id[col + 1];
+        }
+    g.u[D - 1] = 0.0;
+    g.id[D - 1] = -1;
+    --g.q;
+#pragma unroll
+    for (int k = 0; k < D - 1; ++k)
+        if (k >= lpos && k < g.q) {
+            const double a = g.Rm[k][k], b = g.Rm[k + 1][k];
+            const double hh = sqrt(fma(a, a, b * b));
+            if (hh > 0.0) {
+                const double ih = 1.0 / hh;
+                const double cs = a * ih, sn = b * ih;
+#pragma unroll
+                for (int col = 0; col < D; ++col)
+                    if (col >= k) {
+                        // (the sub-diagonal entry b is annihilated; it is never read again)
+                        const double a1 = g.Rm[k][col], a2 = (col > k) ? g.Rm[k + 1][col] : b;
+                        g.Rm[k][col] = fma(cs, a1, sn * a2);
+                        if (col > k) g.Rm[k + 1][col] = fma(-sn, a1, cs * a2);
+                    }
+#pragma unroll
+                for (int i = 0; i < D; ++i) {
+                    const double a1 = g.J[i][k], a2 = g.J[i][k + 1];
+                    g.J[i][k] = fma(cs, a1, sn * a2);
+                    g.J[i][k + 1] = fma(-sn, a1, cs * a2);
+                }
+            }
+        }
+}
+
+// J, R from the ids of the active columns (u, v, id, q are kept): QR of <= D normals.
+template <int D, class Rows>
+MPCCBF_HD void gi_rebuild(GIState<D>& g, const Rows& rows) {
+    const int q = g.q;
+    gi_reset_factor<D>(g);
+    g.q = 0;
+#pragma unroll
+    for (int c = 0; c < D; ++c)
+        if (c < q) {
+            double np[D], rhs, d[D];
+            rows.normal(g.id[c], np, rhs);
+            gi_project<D>(g, np, d);
+            gi_add_column<D>(g, d);
+        }
 }
 
 // Rows must provide:
 //   void scan(const double (&v)[D], double& best, int& best_id) const;   best_id < 0: feasible;
 //        best = +inf flags a violated row that does not depend on v (infeasible)
 //   void normal(int id, double (&np)[D], double& rhs) const;             row  np.v >= rhs
+// and, for SOFT = true,
+//   int group(int id) const;            group of a row (-1: hard row)
+//   double weight(int group) const;     w_j
+//   void set_leader(int group, int id) const;   the piece `id` becomes the leader of its group
 // Returns a SolveStatus code; n_iter is incremented per active-set step.
-template <int D, class Rows>
-__host__ __device__ int gi_run(GIState<D>& g, const Rows& rows, int max_iter, int& n_iter) {
+template <int D, bool SOFT, class Rows>
+__host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, int max_iter, int& n_iter) {
     const double kInfD = HUGE_VAL;
     for (;;) {
         double best = 0.0;
@@ -58,19 +197,18 @@ __host__ __device__ int gi_run(GIState<D>& g, const Rows& rows, int max_iter, in
         if (!(best < kInfD)) return MPCCBF_STATUS_INFEASIBLE;
         double np[D], rhs;
         rows.normal(best_id, np, rhs);
+        int pgrp = -1;
+        double pcap = kInfD;
+        if constexpr (SOFT) {
+            pgrp = rows.group(best_id);
+            if (pgrp >= 0) pcap = rows.weight(pgrp);
+        }
 
         double up_mult = 0.0;
         for (;;) {
             if (++n_iter > max_iter) return MPCCBF_STATUS_ERROR;
-            // d = J' n+
             double d[D];
-#pragma unroll
-            for (int j = 0; j < D; ++j) {
-                double s = 0.0;
-#pragma unroll
-                for (int i = 0; i < D; ++i) s = fma(g.J[i][j], np[i], s);
-                d[j] = s;
-            }
+            gi_project<D>(g, np, d);
             // z = J2 d2, |d2|^2, |d|^2
             double z[D];
 #pragma unroll
@@ -112,7 +250,38 @@ __host__ __device__ int gi_run(GIState<D>& g, const Rows& rows, int max_iter, in
 #pragma unroll
             for (int i = 0; i < D; ++i) sp = fma(np[i], g.v[i], sp);
             const double t2 = z_zero ? kInfD : (-sp / ztn);
-            const double t = fmin(t1, t2);
+            // third rule: a group's multiplier sum reaches its weight
+            double t3 = kInfD;
+            int g3 = -1;
+            if constexpr (SOFT) {
+                // entries: the entering row (rate +1, multiplier up_mult) and the active columns (rate -rr)
+#pragma unroll
+                for (int e = -1; e < D; ++e) {
+                    const int ge = (e < 0) ? pgrp : ((e < g.q) ? gs.grp[e] : -1);
+                    if (ge < 0) continue;
+                    bool first = !(e >= 0 && pgrp == ge);
+#pragma unroll
+                    for (int f = 0; f < D; ++f)
+                        if (f < e && f < g.q && gs.grp[f] == ge) first = false;
+                    if (!first) continue;
+                    double sum = (pgrp == ge) ? up_mult : 0.0, rate = (pgrp == ge) ? 1.0 : 0.0;
+#pragma unroll
+                    for (int f = 0; f < D; ++f)
+                        if (f < g.q && gs.grp[f] == ge) {
+                            sum += g.u[f];
+                            rate -= rr[f];
+                        }
+                    const double w = (e < 0) ? pcap : gs.cap[e];
+                    if (rate > 0.0) {
+                        const double tt = fmax(w - sum, 0.0) / rate;
+                        if (tt < t3) {
+                            t3 = tt;
+                            g3 = ge;
+                        }
+                    }
+                }
+            }
+            const double t = fmin(fmin(t1, t2), t3);
             if (!(t < kInfD)) return MPCCBF_STATUS_INFEASIBLE;
             if (!z_zero) {
 #pragma unroll
@@ -123,73 +292,77 @@ __host__ __device__ int gi_run(GIState<D>& g, const Rows& rows, int max_iter, in
                 if (j < g.q) g.u[j] = fma(-t, rr[j], g.u[j]);
             up_mult += t;
 
-            if (!z_zero && t2 <= t1) {
-                // full step: add the row. Rotate d2 onto e_q (Givens from the bottom), carry J2.
-#pragma unroll
-                for (int k = D - 1; k >= 1; --k) {
-                    if (k > g.q) {
-                        const double a = d[k - 1], b = d[k];
-                        const double hh = sqrt(fma(a, a, b * b));
-                        if (hh > 0.0) {
-                            const double ih = 1.0 / hh;
-                            const double cs = a * ih, sn = b * ih;
-                            d[k - 1] = hh;
-                            d[k] = 0.0;
-#pragma unroll
-                            for (int i = 0; i < D; ++i) {
-                                const double a1 = g.J[i][k - 1], a2 = g.J[i][k];
-                                g.J[i][k - 1] = fma(cs, a1, sn * a2);
-                                g.J[i][k] = fma(-sn, a1, cs * a2);
-                            }
-                        }
-                    }
-                }
+            if (!z_zero && t2 <= t1 && t2 <= t3) {
+                // full step: add the row
 #pragma unroll
                 for (int col = 0; col < D; ++col)
                     if (col == g.q) {
-#pragma unroll
-                        for (int i = 0; i <= col; ++i) g.Rm[i][col] = d[i];
                         g.u[col] = up_mult;
-                    }
-                ++g.q;
-                break;
-            }
-            // partial (or dual-only) step: drop active row lpos
-#pragma unroll
-            for (int col = 0; col < D - 1; ++col)
-                if (col >= lpos) {
-#pragma unroll
-                    for (int i = 0; i <= col + 1; ++i) g.Rm[i][col] = g.Rm[i][col + 1];  // Hessenberg part
-                    g.u[col] = g.u[col + 1];
-                }
-            g.u[D - 1] = 0.0;
-            --g.q;
-#pragma unroll
-            for (int k = 0; k < D - 1; ++k)
-                if (k >= lpos && k < g.q) {
-                    const double a = g.Rm[k][k], b = g.Rm[k + 1][k];
-                    const double hh = sqrt(fma(a, a, b * b));
-                    if (hh > 0.0) {
-                        const double ih = 1.0 / hh;
-                        const double cs = a * ih, sn = b * ih;
-#pragma unroll
-                        for (int col = 0; col < D; ++col)
-                            if (col >= k) {
-                                // (the sub-diagonal entry b is annihilated; it is never read again)
-                                const double a1 = g.Rm[k][col], a2 = (col > k) ? g.Rm[k + 1][col] : b;
-                                g.Rm[k][col] = fma(cs, a1, sn * a2);
-                                if (col > k) g.Rm[k + 1][col] = fma(-sn, a1, cs * a2);
-                            }
-#pragma unroll
-                        for (int i = 0; i < D; ++i) {
-                            const double a1 = g.J[i][k], a2 = g.J[i][k + 1];
-                            g.J[i][k] = fma(cs, a1, sn * a2);
-                            g.J[i][k + 1] = fma(-sn, a1, cs * a2);
+                        g.id[col] = best_id;
+                        if constexpr (SOFT) {
+                            gs.grp[col] = pgrp;
+                            gs.cap[col] = pcap;
                         }
                     }
+                gi_add_column<D>(g, d);
+                break;
+            }
+            if constexpr (SOFT) if (t3 <= t1) {
+                // group g3 is at its weight: the leadership passes to the active row of the group with the
+                // largest multiplier, or to the entering row when the group has no active row
+                int a = -1;
+                double ua = -1.0;
+#pragma unroll
+                for (int c = 0; c < D; ++c)
+                    if (c < g.q && gs.grp[c] == g3 && g.u[c] > ua) {
+                        a = c;
+                        ua = g.u[c];
+                    }
+                if (a < 0) {  // no active row in the group: it is the entering row's own group
+                    rows.set_leader(g3, best_id);  // absorbed by its slack
+                    break;
                 }
+                int aid = -1;
+#pragma unroll
+                for (int c = 0; c < D; ++c)
+                    if (c == a) aid = g.id[c];
+                rows.set_leader(g3, aid);
+#pragma unroll
+                for (int c = 0; c < D - 1; ++c)
+                    if (c >= a) {
+                        g.u[c] = g.u[c + 1];
+                        g.id[c] = g.id[c + 1];
+                        gs.grp[c] = gs.grp[c + 1];
+                        gs.cap[c] = gs.cap[c + 1];
+                    }
+                g.u[D - 1] = 0.0;
+                g.id[D - 1] = -1;
+                gs.grp[D - 1] = -1;
+                --g.q;
+                gi_rebuild<D>(g, rows);  // the group's other active rows are now expressed against the new leader
+                if (pgrp == g3) rows.normal(best_id, np, rhs);
+                continue;
+            }
+            // partial (or dual-only) step: drop active row lpos
+            if constexpr (SOFT) {
+#pragma unroll
+                for (int c = 0; c < D - 1; ++c)
+                    if (c >= lpos) {
+                        gs.grp[c] = gs.grp[c + 1];
+                        gs.cap[c] = gs.cap[c + 1];
+                    }
+                gs.grp[D - 1] = -1;
+            }
+            gi_drop_column<D>(g, lpos);
         }
     }
+}
+
+// hard rows only
+template <int D, class Rows>
+__host__ __device__ int gi_run(GIState<D>& g, const Rows& rows, int max_iter, int& n_iter) {
+    GISoft<D> gs;
+    return gi_run<D, false, Rows>(g, gs, rows, max_iter, n_iter);
 }
 
 }  // namespace mpccbf

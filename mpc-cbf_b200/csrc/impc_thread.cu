@@ -176,7 +176,39 @@ struct RowsAxis {
     }
 };
 
+// slack_cost * slack_decay^rank, rank of neighbour j among the J neighbours by distance to the ego agent
+// (closest first, ties by index; ConnectivityIMPCCBF.cpp:76-100). Near-ties decide ranks in symmetric
+// formations: the same double arithmetic as the host code of the reference (separately rounded products
+// and sum, no fma), exact ties by index.
+#ifdef __CUDA_ARCH__
+#define TSQSUM(x, y) __dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y))
+#else
+static inline double tsqsum_host(double x, double y) {
+    volatile double a = x * x, b = y * y;
+    return a + b;
+}
+#define TSQSUM(x, y) tsqsum_host(x, y)
+#endif
+MPCCBF_HD double slack_weight(const double* st, int self, int j, int J, double cost, double decay) {
+    const double* me = st + self * 6;
+    const int other = j + (j >= self ? 1 : 0);
+    const double dx = st[other * 6] - me[0], dy = st[other * 6 + 1] - me[1];
+    const double dj = sqrt(TSQSUM(dx, dy));
+    int rank = 0;
+    for (int i = 0; i < J; ++i) {
+        const int oi = i + (i >= self ? 1 : 0);
+        const double ex = st[oi * 6] - me[0], ey = st[oi * 6 + 1] - me[1];
+        const double di = sqrt(TSQSUM(ex, ey));
+        rank += (di < dj || (di == dj && i < j)) ? 1 : 0;
+    }
+    return cost * pow(decay, static_cast<double>(rank));
+}
+
 // ---- x/y: bound rows of both axes + the candidate safety rows, 4 dof -----------------------------
+// SOFT (slack mode): the safety rows of neighbour nb form a group with one slack (gi_solver.h). Row ids
+// are then nid_fix + nb * (hit + 1) + kk with kk < hit the row of horizon step kk and kk == hit the
+// piece "none"; lead[nb] = 0 while the group's slack is zero, else 1 + the horizon step of its leader.
+template <bool SOFT>
 struct RowsXY {
     const double* tm;
     int K;
@@ -195,6 +227,10 @@ struct RowsXY {
     const double (*pq)[4];  // polynomial row structure (DevTables::poly)
     const double* scn;      // [K][4] key-scan table
     const double* lim;      // [axis x, y]{midA, halfA, midV, halfV}
+    // slack mode
+    unsigned char* lead;  // [N-1] leaders of this agent's groups
+    int nnb;              // N - 1
+    double slack_cost, slack_decay;
 
     MPCCBF_HD void cbf_row(int j, double& ax, double& ay, double& b, int& k) const {
         const int nb = j / hit;
@@ -204,21 +240,59 @@ struct RowsXY {
         const double* e = pred + (k * 4) * pstride;
         hocbf_row(e[0], e[pstride], e[2 * pstride], e[3 * pstride], o[0], o[1], o[3], o[4], dmin2, gamma, ax, ay, b);
     }
+    // g(v) = rhs - n.v of safety row j: positive when violated
+    MPCCBF_HD double cbf_g(const double (&v)[4], double ax, double ay, double b, int k) const {
+        const double* t = tm + (2 * K + k) * kTmplStride;
+        const double accx = fma(t[0], v[0], fma(t[1], v[1], fma(t[2], s[0][0], t[3] * s[0][1])));
+        const double accy = fma(t[0], v[2], fma(t[1], v[3], fma(t[2], s[1][0], t[3] * s[1][1])));
+        return -(fma(ax, accx, fma(ay, accy, b)));
+    }
     MPCCBF_HD void check_cbf(int j, const double (&v)[4], int& key, int& jbest) const {
         double ax, ay, b;
         int k;
         cbf_row(j, ax, ay, b, k);
         const double* t = tm + (2 * K + k) * kTmplStride;
-        const double accx = fma(t[0], v[0], fma(t[1], v[1], fma(t[2], s[0][0], t[3] * s[0][1])));
-        const double accy = fma(t[0], v[2], fma(t[1], v[3], fma(t[2], s[1][0], t[3] * s[1][1])));
-        const double viol = -(fma(ax, accx, fma(ay, accy, b)));
-        if (viol > tol * fmax(1.0, fabs(b)) && fabs(b) < 1e20) {
+        const double g = cbf_g(v, ax, ay, b, k);
+        if (!(fabs(b) < 1e20)) return;
+        if constexpr (!SOFT) {
+            if (g > tol * fmax(1.0, fabs(b))) {
+                const double an2 = fma(ax, ax, ay * ay);
+                const double score = (an2 > 0.0) ? g * t[4] * TRSQRT(an2) : HUGE_VAL;
+                const int kk = HIWORD(score) & kKeyMask;
+                if (kk > key) {
+                    key = kk;
+                    jbest = j;
+                }
+            }
+            return;
+        }
+        // a violated soft row that does not depend on v is taken up by its slack: large finite score
+        const int nb = j / hit;
+        const int ld = lead[nb];
+        double viol, thr = tol * fmax(1.0, fabs(b)), score;
+        int id = nb * (hit + 1) + k;
+        if (ld == 0 || ld == k + 1) {
+            viol = ld ? -g : g;  // the leader itself: piece "none" is violated once the row holds again
+            if (ld) id = nb * (hit + 1) + hit;
             const double an2 = fma(ax, ax, ay * ay);
-            const double score = (an2 > 0.0) ? viol * t[4] * TRSQRT(an2) : HUGE_VAL;
+            score = (an2 > 0.0) ? viol * t[4] * TRSQRT(an2) : 1e150;
+        } else {
+            double axl, ayl, bl;
+            int kl;
+            cbf_row(nb * hit + ld - 1, axl, ayl, bl, kl);
+            const double* tl = tm + (2 * K + kl) * kTmplStride;
+            viol = g - cbf_g(v, axl, ayl, bl, kl);
+            thr = tol * fmax(fmax(1.0, fabs(b)), fabs(bl));
+            const double d0 = ax * t[0] - axl * tl[0], d1 = ax * t[1] - axl * tl[1];
+            const double d2 = ay * t[0] - ayl * tl[0], d3 = ay * t[1] - ayl * tl[1];
+            const double nn = fma(d0, d0, fma(d1, d1, fma(d2, d2, d3 * d3)));
+            score = (nn > 0.0) ? viol * TRSQRT(nn) : 1e150;
+        }
+        if (viol > thr) {
             const int kk = HIWORD(score) & kKeyMask;
             if (kk > key) {
                 key = kk;
-                jbest = j;
+                jbest = id;
             }
         }
     }
@@ -257,6 +331,20 @@ struct RowsXY {
         const double h = dsel ? (ax ? hi[1][1] : hi[1][0]) : (ax ? hi[0][1] : hi[0][0]);
         if (val - h > l - val) best_id |= 1;
     }
+    // sg * (normal, rhs) of safety row j accumulated into (np, rhs)
+    MPCCBF_HD void add_cbf_normal(int j, double sg, double (&np)[4], double& rhs) const {
+        double ax, ay, b;
+        int k;
+        cbf_row(j, ax, ay, b, k);
+        const double* t = tm + (2 * K + k) * kTmplStride;
+        np[0] = fma(sg * ax, t[0], np[0]);
+        np[1] = fma(sg * ax, t[1], np[1]);
+        np[2] = fma(sg * ay, t[0], np[2]);
+        np[3] = fma(sg * ay, t[1], np[3]);
+        const double offx = fma(t[2], s[0][0], t[3] * s[0][1]);
+        const double offy = fma(t[2], s[1][0], t[3] * s[1][1]);
+        rhs -= sg * (b + ax * offx + ay * offy);
+    }
     MPCCBF_HD void normal(int id, double (&np)[4], double& rhs) const {
         if (id < nid_fix) {
             const bool up = id & 1;
@@ -278,18 +366,38 @@ struct RowsXY {
             np[3] = ax ? n1 : 0.0;
             rhs = sg * (bound - fma(t[2], sa, t[3] * sb));
         } else {
+            np[0] = np[1] = np[2] = np[3] = 0.0;
+            rhs = 0.0;
+            if constexpr (!SOFT) {
+                add_cbf_normal(id - nid_fix, 1.0, np, rhs);
+            } else {
+                const int jj = id - nid_fix;
+                const int nb = jj / (hit + 1), kk = jj - nb * (hit + 1);
+                const int ld = lead[nb];
+                if (kk < hit) add_cbf_normal(nb * hit + kk, 1.0, np, rhs);
+                if (ld) add_cbf_normal(nb * hit + ld - 1, -1.0, np, rhs);
+            }
+        }
+    }
+    // ---- group interface of gi_run<.., SOFT = true> ------------------------------------------------------
+    MPCCBF_HD int group(int id) const { return id < nid_fix ? -1 : (id - nid_fix) / (hit + 1); }
+    MPCCBF_HD double weight(int grp) const { return slack_weight(st, self, grp, nnb, slack_cost, slack_decay); }
+    MPCCBF_HD void set_leader(int grp, int id) const {
+        const int kk = (id - nid_fix) - grp * (hit + 1);
+        lead[grp] = static_cast<unsigned char>(kk < hit ? kk + 1 : 0);
+    }
+    // sum_j w_j s_j at v, s_j = max(0, g of the group's leader) (groups without a leader have s_j = 0)
+    MPCCBF_HD double penalty(const double (&v)[4]) const {
+        double pen = 0.0;
+        for (int nb = 0; nb < nnb; ++nb) {
+            const int ld = lead[nb];
+            if (!ld) continue;
             double ax, ay, b;
             int k;
-            cbf_row(id - nid_fix, ax, ay, b, k);
-            const double* t = tm + (2 * K + k) * kTmplStride;
-            np[0] = ax * t[0];
-            np[1] = ax * t[1];
-            np[2] = ay * t[0];
-            np[3] = ay * t[1];
-            const double offx = fma(t[2], s[0][0], t[3] * s[0][1]);
-            const double offy = fma(t[2], s[1][0], t[3] * s[1][1]);
-            rhs = -(b + ax * offx + ay * offy);
+            cbf_row(nb * hit + ld - 1, ax, ay, b, k);
+            pen = fma(weight(nb), fmax(cbf_g(v, ax, ay, b, k), 0.0), pen);
         }
+        return pen;
     }
 };
 
@@ -303,11 +411,13 @@ struct AgentCtx {
     unsigned short* cand;             // [i * cstride]
     int pstride, cstride;
     double* sol;                      // [kSolStride] result record of this agent
+    unsigned char* lead;              // [N-1] group leaders of this agent (slack mode), else NULL
 };
 
 // keeps the safety rows that can be violated somewhere inside the acceleration box (a row that
 // holds on the whole box holds at every point the bound rows admit, so dropping it is exact)
-MPCCBF_HD void build_candidates(RowsXY& rx, const DevTables& T, unsigned short* cand, int cstride) {
+template <bool SOFT>
+MPCCBF_HD void build_candidates(RowsXY<SOFT>& rx, const DevTables& T, unsigned short* cand, int cstride) {
     int nc = 0;
     const bool wide = rx.ncbf > 65535;
     for (int j = 0; j < rx.ncbf && !wide; ++j) {
@@ -330,6 +440,7 @@ MPCCBF_HD double ctrl_point(const double* y, int ax, const double* sol) {
 }
 
 // Everything optimize() does for agent-QP g (one thread).
+template <bool SOFT>
 __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int g, int self, const AgentCtx& c) {
     const int K = T.K, N = T.N, H = T.H;
     double s[3][2];
@@ -389,7 +500,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         base_status = gi_run<2>(gy, ry, T.max_gi, total_iter);
     }
     // ---- x/y stage A: bound rows only ---------------------------------------------------------
-    RowsXY rx;
+    RowsXY<SOFT> rx;
     rx.tm = c.tm;
     rx.K = K;
 #pragma unroll
@@ -418,12 +529,22 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     rx.pq = c.pq;
     rx.scn = c.scn;
     rx.lim = c.lim;
+    rx.lead = c.lead;
+    rx.nnb = N - 1;
+    rx.slack_cost = T.slack_cost;
+    rx.slack_decay = T.slack_decay;
     GIState<4> gx;
+    GISoft<4> gs;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        gs.grp[i] = -1;
+        gs.cap[i] = HUGE_VAL;
+    }
     gi_init<4>(gx, v0);
-    GIState<4> snap;  // stage-A factorisation; its address escapes so that it lives in local memory
-#ifdef __CUDA_ARCH__
-    asm volatile("" ::"l"(&snap) : "memory");
-#endif
+    // stage-A solution: iterate, multipliers and ids of its active bound rows (the factorisation is
+    // rebuilt from the ids when a later IMPC iteration has to start from it again)
+    double snap_v[4], snap_u[4];
+    int snap_id[4], snap_q = 0;
 
     // Phase machine with ONE gi_run<4> call site (the unrolled 4-dof active-set code is the bulk of
     // the kernel's instruction footprint; inlining it once keeps the kernel inside the instruction
@@ -433,6 +554,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     int n_ok = 0;
     bool dirty = false;  // gx has safety rows in its active set (not reusable as stage A)
     double vlast[6] = {0, 0, 0, 0, 0, 0};
+    double pen_last = 0.0;  // slack mode: sum_j w_j s_j of the last successful iterate
     const size_t sbase = static_cast<size_t>(g) * T.iters;
     int mode = kStageA, it = 0, it_iter = 0;
     while (it < T.iters) {
@@ -460,23 +582,41 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                         }
                     }
                 }
-                if (dirty) gx = snap;
+                if (dirty) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        gx.v[i] = snap_v[i];
+                        gx.u[i] = snap_u[i];
+                        gx.id[i] = snap_id[i];
+                        if constexpr (SOFT) gs.grp[i] = -1;
+                    }
+                    gx.q = snap_q;
+                    gi_rebuild<4>(gx, rx);
+                }
                 dirty = false;
                 rx.hit = hit;
                 rx.ncbf = (N - 1) * hit;
-                build_candidates(rx, T, c.cand, c.cstride);
+                if constexpr (SOFT)
+                    for (int nb = 0; nb < N - 1; ++nb) c.lead[nb] = 0;
+                build_candidates<SOFT>(rx, T, c.cand, c.cstride);
                 run = rx.ncand != 0;
             } else {
                 run = true;
             }
         }
         int n2 = 0;
-        if (run) stat = gi_run<4>(gx, rx, T.max_gi, n2);
+        if (run) stat = gi_run<4, SOFT>(gx, gs, rx, T.max_gi, n2);
         it_iter += n2;
         if (mode == kStageA) {
             base_status = stat;
             it_iter += total_iter;  // yaw iterations are booked on IMPC iteration 0
-            snap = gx;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                snap_v[i] = gx.v[i];
+                snap_u[i] = gx.u[i];
+                snap_id[i] = gx.id[i];
+            }
+            snap_q = gx.q;
             mode = kIter;
             continue;
         }
@@ -496,6 +636,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         for (int i = 0; i < 4; ++i) vlast[i] = gx.v[i];
         vlast[4] = gy.v[0];
         vlast[5] = gy.v[1];
+        if constexpr (SOFT) pen_last = (run && a.objective) ? rx.penalty(gx.v) : 0.0;
         if (a.v_all) {  // slack-mode verification reads the iterates in whitened coordinates
             double* vo = a.v_all + (sbase + it) * 6;
 #pragma unroll
@@ -538,7 +679,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                 dd = fma(e, e, dd);
                 nn = fma(v0[i], v0[i], nn);
             }
-            obj = 0.5 * dd - 0.5 * nn + c0;
+            obj = 0.5 * dd - 0.5 * nn + c0 + pen_last;
         }
         a.objective[g] = obj;
     }
@@ -586,6 +727,7 @@ static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count) {
     return L;
 }
 
+template <bool SOFT>
 __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kernel(const DevTables T, const StepArgs a, const ThreadSmemLayout L) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* tm = reinterpret_cast<double*>(smem_raw);
@@ -649,7 +791,8 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
             c.cand = wcand + lane;
             c.cstride = 32;
             c.sol = wsol + lane * kSolStride;
-            agent_thread(T, a, g, self, c);
+            c.lead = SOFT ? a.lead_ws + static_cast<size_t>(g) * (N - 1) : nullptr;
+            agent_thread<SOFT>(T, a, g, self, c);
         }
         __syncwarp();
         {   // control points of the last successful iterate: coalesced stores, whole warp
@@ -672,6 +815,7 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
     std::vector<double> pred(static_cast<size_t>(std::max(T.H, 1)) * 4), sol(kSolStride);
     std::vector<unsigned short> cand(kCandMax);
     std::vector<double> lim(12), scn(static_cast<size_t>(4) * T.K);
+    std::vector<unsigned char> lead(static_cast<size_t>(std::max(T.N, 1)));
     fill_scan_tables(T, T.tmpl, lim.data(), scn.data(), 0, 1);
     for (int g = 0; g < a.num_qp; ++g) {
         const int scen = g / a.agent_count;
@@ -687,7 +831,11 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
         c.cand = cand.data();
         c.cstride = 1;
         c.sol = sol.data();
-        agent_thread(T, a, g, self, c);
+        c.lead = lead.data();
+        if (T.slack)
+            agent_thread<true>(T, a, g, self, c);
+        else
+            agent_thread<false>(T, a, g, self, c);
         double* out = a.ctrl_pts + static_cast<size_t>(g) * T.n;
         for (int i = 0; i < T.n; ++i) {
             const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
@@ -709,17 +857,19 @@ int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cuda
         smem = L.shared_bytes + L.warp_bytes * (threads / 32);
     }
     if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
-    cudaError_t e = cudaFuncSetAttribute(impc_thread_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (T.slack && !a.lead_ws) return cudaErrorInvalidValue;
+    auto kern = T.slack ? impc_thread_kernel<true> : impc_thread_kernel<false>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return e;
     int per_sm = 1;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, impc_thread_kernel, threads, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) per_sm = 1;
     const int ntiles = (a.num_qp + 31) / 32;
     const int need = (ntiles + threads / 32 - 1) / (threads / 32);
     int grid = sm_count * per_sm;  // persistent: a multiple of the SM count
     if (need < grid) grid = need;
-    impc_thread_kernel<<<grid, threads, smem, stream>>>(T, a, L);
+    kern<<<grid, threads, smem, stream>>>(T, a, L);
     return cudaGetLastError();
 }
 

@@ -22,6 +22,7 @@ struct StepArgs {
     int32_t* n_curves;       // [B]   may be NULL
     double* objective;       // [B]   may be NULL
     int32_t* gi_iters;       // [B][iters] may be NULL
+    unsigned char* lead_ws = nullptr;  // [B][N-1] slack mode: group leaders (kernel scratch)
     int32_t num_qp;          // B = scenarios * agent_count
     int32_t agent_begin;     // first agent of each scenario handled by this launch
     int32_t agent_count;     // agents per scenario handled by this launch
@@ -87,31 +88,6 @@ int dense_qp_solve_device(const DenseOpts& opts, int32_t batch, int32_t n, int32
                           const double* A, const double* l, const double* u, double* wsP, double* wsA, double* x,
                           double* objective, int32_t* status, int32_t* iters);
 
-// Slack-mode controller path (slack_path.cu): reduced (6 + N-1)-variable QPs assembled on the device
-// and solved by the dense kernel. The workspace belongs to the handle and grows on demand.
-struct SlackWorkspace {
-    size_t cap_qps = 0;     // QPs the buffers below hold
-    int nv = 0, m_max = 0;  // shape they were sized for
-    double *P = nullptr, *q = nullptr, *A = nullptr, *l = nullptr, *u = nullptr, *wsP = nullptr, *wsA = nullptr;
-    double *x = nullptr, *obj = nullptr, *pred = nullptr, *vlast = nullptr, *objlast = nullptr, *c0 = nullptr;
-    int32_t *stat = nullptr, *it = nullptr, *nok = nullptr;
-    // first tier (hard-row solve + verification): iterates of the fused kernels, agents for the ADMM tier
-    size_t hard_cap = 0;
-    double* hard_all = nullptr;   // [hard_cap][iters][6] whitened iterates of the hard-row solve
-    int32_t* list = nullptr;      // [hard_cap]
-    int32_t* count = nullptr;     // device counter
-    int32_t* h_count = nullptr;   // pinned host copy
-};
-// ADMM tier for the QPs in `list` (device array of `count` QP indices), or for all of `a` when list is NULL.
-int slack_step(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, const DenseOpts& o, SlackWorkspace& w,
-               const int32_t* list, int count, int64_t* launches);
-// Buffers of the first tier for `num_qp` agents; then, after the fused hard-row kernels ran with
-// v_all = w.hard_all, the verification: fills w.list and returns the number of agents in *n_fallback
-// (synchronises the stream).
-int slack_prepare_hard(const DevTables& T, int num_qp, SlackWorkspace& w);
-int slack_verify(const DevTables& T, const mpccbf_config& cfg, const StepArgs& a, SlackWorkspace& w, int sm_count,
-                 cudaStream_t stream, int* n_fallback);
-void slack_free(SlackWorkspace& w);
 void set_error(const std::string& msg);
 #ifdef MPCCBF_HOST_EMUL
 void emul_impc_reduced_host(const DevTables& T, const StepArgs& a);

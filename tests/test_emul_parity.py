@@ -109,3 +109,24 @@ def test_bound_rows_active_everywhere(M, O, emul, K, p, monkeypatch):
     full = run_emul(M, emul, cfg, st, tg)
     assert np.array_equal(full["status"], got["status"])
     assert np.abs(full["ctrl_pts"] - got["ctrl_pts"]).max() < 1e-9
+
+
+@pytest.mark.parametrize("extra,N,S,spread", [
+    (dict(), 16, 24, 1.15),
+    (dict(cbf_horizon=3), 16, 12, 1.1),
+    (dict(cbf_horizon=4, slack_cost=5.0, slack_decay=0.7), 9, 16, 1.05),
+    (dict(slack_cost=100.0, slack_decay=0.5), 16, 12, 1.05),
+    (dict(slack_cost=0.05, slack_decay=0.9, impc_iter=4), 12, 12, 1.0),
+])
+def test_slack_mode_capped_multipliers(M, O, emul, extra, N, S, spread):
+    # cbf_params.slack_mode: the capped-multiplier active-set iteration of gi_solver.h against the oracle's
+    # full-space QP with slack variables (ConnectivityIMPCCBF.cpp:76-100, MPCCBFQPGeneratorBase.cpp:28-38,80-135)
+    base = dict(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N, slack_mode=1, slack_cost=50000.0, slack_decay=0.1)
+    base.update(extra)
+    cfg, oc = M.default_config(**base), O.base_config(**base)
+    st, tg = dense_scenarios(S, N, 40 + N, 0.8, spread=spread, vmax=1.0)
+    st[0, 1, 3] = 2.6  # the bound rows stay hard: |v0| > v_max is still infeasible
+    got = run_emul(M, emul, cfg, st, tg)
+    check_step(O, oc, O.get_table(oc, "U_basis"), st, tg, got, check_viol_max=0)
+    assert list(got["status"][0, 1]) == [M.STATUS_INFEASIBLE] + [M.STATUS_SKIPPED] * (cfg.impc_iter - 1)
+    assert (got["status"] == M.STATUS_OPTIMAL).mean() > 0.95
