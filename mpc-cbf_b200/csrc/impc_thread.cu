@@ -104,35 +104,42 @@ static inline int hiword_host(double x) {
 }
 #define HIWORD(x) hiword_host(x)
 #endif
-MPCCBF_HD void scan_axis_keys(const double* scn, int K, const AxisPoly& a, double midA, double halfA, double midV,
+// The scan does not walk the horizon. Along the horizon the acceleration row value is affine in t_k and
+// the velocity row value quadratic, and the thresholded bounds are the same at every k, so
+// max_k |val_k - mid| is attained at an end sample or (velocity) at a sample next to the parabola's
+// vertex: "is any row violated" is decided exactly by 2 + 5 samples per axis instead of 2 K, and the
+// pivot is the candidate with the largest violation in whitened distance (any violated row is a valid
+// pivot of the dual active-set iteration; the minimiser does not depend on the choice).
+// scn[k] = {t_k, inv_norm_acc, inv_norm_vel, -}; kinv = (K - 1) / t_{K-1} maps a time to a sample index.
+MPCCBF_HD int key_acc(const double* scn, int k, const AxisPoly& a, double a0, double halfA) {
+    const double tk = scn[4 * k], ia = scn[4 * k + 1];
+    const double sa = (fabs(fma(a.p[1], tk, a0)) - halfA) * ia;
+    return (HIWORD(sa) & kKeyMask) | k;
+}
+MPCCBF_HD int key_vel(const double* scn, int k, const AxisPoly& a, double v0, double halfV) {
+    const double tk = scn[4 * k], iv = scn[4 * k + 2];
+    const double sv = (fabs(fma(fma(a.p[4], tk, a.p[3]), tk, v0)) - halfV) * iv;
+    return (HIWORD(sv) & kKeyMask) | k;
+}
+// sample index next to the vertex of vel(t) = p2 + p3 t + p4 t^2, clamped to [1, K - 2] (float precision
+// is ample: the three samples kv - 1, kv, kv + 1 are all evaluated)
+MPCCBF_HD int vertex_sample(const AxisPoly& a, float kinv, int K) {
+    const float tv = -0.5f * static_cast<float>(a.p[3]) / static_cast<float>(a.p[4]);  // +-inf / NaN when p4 = 0
+    const float kf = fminf(fmaxf(tv * kinv, 1.0f), static_cast<float>(K - 2));         // NaN -> 1
+    return static_cast<int>(kf + 0.5f);
+}
+MPCCBF_HD void scan_axis_keys(const double* scn, int K, float kinv, const AxisPoly& a, double midA, double halfA, double midV,
                               double halfV, int& keyA, int& keyV) {
     const double a0 = a.p[0] - midA, v0 = a.p[2] - midV;
-#pragma unroll 4
-    for (int k = 0; k < K; ++k) {
-        const double tk = scn[4 * k], ia = scn[4 * k + 1], iv = scn[4 * k + 2];
-        const double sa = (fabs(fma(a.p[1], tk, a0)) - halfA) * ia;
-        const double sv = (fabs(fma(fma(a.p[4], tk, a.p[3]), tk, v0)) - halfV) * iv;
-        keyA = max(keyA, (HIWORD(sa) & kKeyMask) | k);
-        keyV = max(keyV, (HIWORD(sv) & kKeyMask) | k);
-    }
+    keyA = max(keyA, max(key_acc(scn, 0, a, a0, halfA), key_acc(scn, K - 1, a, a0, halfA)));
+    const int kv = vertex_sample(a, kinv, K);
+    keyV = max(keyV, max(key_vel(scn, 0, a, v0, halfV), key_vel(scn, K - 1, a, v0, halfV)));
+    keyV = max(keyV, max(key_vel(scn, kv - 1, a, v0, halfV), max(key_vel(scn, kv, a, v0, halfV), key_vel(scn, kv + 1, a, v0, halfV))));
 }
-// both x/y axes in one pass over k: four independent chains, one load of scn[k]
-MPCCBF_HD void scan_axes_keys2(const double* scn, int K, const AxisPoly& ax, const AxisPoly& ay, const double* lim, int (&key)[4]) {
-    const double xa0 = ax.p[0] - lim[0], xv0 = ax.p[2] - lim[2];
-    const double ya0 = ay.p[0] - lim[4], yv0 = ay.p[2] - lim[6];
-    const double hxa = lim[1], hxv = lim[3], hya = lim[5], hyv = lim[7];
-#pragma unroll 2
-    for (int k = 0; k < K; ++k) {
-        const double tk = scn[4 * k], ia = scn[4 * k + 1], iv = scn[4 * k + 2];
-        const double s0 = (fabs(fma(ax.p[1], tk, xa0)) - hxa) * ia;
-        const double s1 = (fabs(fma(fma(ax.p[4], tk, ax.p[3]), tk, xv0)) - hxv) * iv;
-        const double s2 = (fabs(fma(ay.p[1], tk, ya0)) - hya) * ia;
-        const double s3 = (fabs(fma(fma(ay.p[4], tk, ay.p[3]), tk, yv0)) - hyv) * iv;
-        key[0] = max(key[0], (HIWORD(s0) & kKeyMask) | k);
-        key[1] = max(key[1], (HIWORD(s1) & kKeyMask) | k);
-        key[2] = max(key[2], (HIWORD(s2) & kKeyMask) | k);
-        key[3] = max(key[3], (HIWORD(s3) & kKeyMask) | k);
-    }
+// both x/y axes: key[ax * 2 + dsel]
+MPCCBF_HD void scan_axes_keys2(const double* scn, int K, float kinv, const AxisPoly& ax, const AxisPoly& ay, const double* lim, int (&key)[4]) {
+    scan_axis_keys(scn, K, kinv, ax, lim[0], lim[1], lim[2], lim[3], key[0], key[1]);
+    scan_axis_keys(scn, K, kinv, ay, lim[4], lim[5], lim[6], lim[7], key[2], key[3]);
 }
 MPCCBF_HD double bound_hi_eff(double hi, double tol) { return fabs(hi) < 1e20 ? hi + tol * fmax(1.0, fabs(hi)) : HUGE_VAL; }
 MPCCBF_HD double bound_lo_eff(double lo, double tol) { return fabs(lo) < 1e20 ? lo - tol * fmax(1.0, fabs(lo)) : -HUGE_VAL; }
@@ -146,12 +153,13 @@ struct RowsAxis {
     double tol;
     const double (*pq)[4];  // polynomial row structure (DevTables::poly)
     const double* scn;      // [K][4] key-scan table
+    float kinv;             // (K - 1) / t_{K-1}
     const double* lim;      // {midA, halfA, midV, halfV} of this axis
 
     MPCCBF_HD void scan(const double (&v)[2], double& best, int& best_id) const {
         const AxisPoly a = axis_poly(pq, v[0], v[1], s0, s1);
         int keyA = 0, keyV = 0;
-        scan_axis_keys(scn, K, a, lim[0], lim[1], lim[2], lim[3], keyA, keyV);
+        scan_axis_keys(scn, K, kinv, a, lim[0], lim[1], lim[2], lim[3], keyA, keyV);
         const int key = max(keyA, keyV);
         if (key < 128) return;  // no row violated
         const int dsel = (keyV > keyA) ? 1 : 0, k = key & 127;
@@ -226,6 +234,7 @@ struct RowsXY {
     int nid_fix;          // 8K
     const double (*pq)[4];  // polynomial row structure (DevTables::poly)
     const double* scn;      // [K][4] key-scan table
+    float kinv;             // (K - 1) / t_{K-1}
     const double* lim;      // [axis x, y]{midA, halfA, midV, halfV}
     // slack mode
     unsigned char* lead;  // [N-1] leaders of this agent's groups
@@ -301,7 +310,7 @@ struct RowsXY {
         {
             const AxisPoly px = axis_poly(pq, v[0], v[1], s[0][0], s[0][1]);
             const AxisPoly py = axis_poly(pq, v[2], v[3], s[1][0], s[1][1]);
-            scan_axes_keys2(scn, K, px, py, lim, key);
+            scan_axes_keys2(scn, K, kinv, px, py, lim, key);
         }
         int kb = 0, jb = -1;
         if (ncand < 0) {
@@ -480,6 +489,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
             c0 += ps * (T.Kc[0][0] * ps + T.Kc[0][1] * vs) + vs * (T.Kc[1][0] * ps + T.Kc[1][1] * vs) + (k0 * ps + k1 * vs);
         }
     }
+    const float kinv = static_cast<float>((K - 1) / c.scn[4 * (K - 1)]);
     int total_iter = 0;
     // ---- yaw: 2-dof projection, shared by every IMPC iteration --------------------------------
     GIState<2> gy;
@@ -496,6 +506,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         ry.tol = T.feas_tol;
         ry.pq = c.pq;
         ry.scn = c.scn;
+        ry.kinv = kinv;
         ry.lim = c.lim + 8;
         base_status = gi_run<2>(gy, ry, T.max_gi, total_iter);
     }
@@ -528,6 +539,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     rx.nid_fix = 8 * K;
     rx.pq = c.pq;
     rx.scn = c.scn;
+    rx.kinv = kinv;
     rx.lim = c.lim;
     rx.lead = c.lead;
     rx.nnb = N - 1;

@@ -1,7 +1,8 @@
-"""GPU: BASELINE.json's full-size configurations through size-independent properties (the oracle cannot
-finish 131 072 QPs in seconds): feasibility of every returned curve against the reference's own rows,
-bit-exact determinism and scenario-permutation equivariance, agreement of the two kernel variants,
-translation invariance, and oracle parity on a random sample of the batch."""
+"""GPU: BASELINE.json's full-size configurations. Every agent of the batch is compared with the oracle
+(all host threads; double precision for the bulk, long double for the few agents that differ), on tight
+swarms and on the bench's own closed-loop snapshots, plus size-independent properties: feasibility of
+every returned curve against the reference's own rows, bit-exact determinism and scenario-permutation
+equivariance, agreement of the two kernel variants, translation invariance."""
 import numpy as np
 import pytest
 
@@ -43,6 +44,68 @@ def feasibility(O, oc, cfg, st, tg, got):
     return dict(box=box, eq=eq, cbf=cbf, n_ok=int(ok.sum()))
 
 
+def oracle_all(O, oc, st, tg, got, label, feas_tol=1e-9, max_recheck_frac=2e-3):
+    """Every agent of the batch against the oracle: statuses identical, control points within TOL_CONTROL,
+    objective within 1e-6 relative. Bulk in double on all host threads; agents that differ there are solved
+    again in long double (the double run of the oracle has its own rounding at feasibility thresholds)."""
+    S, N = st.shape[:2]
+    ref = O.step_batch(oc, st, tg, threads=O.hardware_threads(), prec=0, feas_tol=feas_tol)
+    err = np.abs(got["ctrl_pts"] - ref["ctrl_pts"]).max(-1)
+    rel = np.abs(got["objective"] - ref["objective"]) / np.maximum(1.0, np.abs(ref["objective"]))
+    bad = (got["status"] != ref["status"]).any(-1) | (err > TOL_CONTROL) | (rel > 1e-6)
+    redo = np.argwhere(bad)
+    assert len(redo) <= max(4, max_recheck_frac * S * N), f"{label}: {len(redo)} agents differ from the double-precision oracle"
+    K = oc.k_hor
+    for s, a in redo:
+        r = O.optimize(oc, st[s], int(a), np.tile(tg[s, a], K), feas_tol=feas_tol, prec=1)
+        assert list(r["status"]) == list(got["status"][s, a]), f"{label}: status of scenario {s} agent {a}: {got['status'][s, a]} vs oracle {r['status']}"
+        if r["n_curves"]:
+            assert np.abs(r["curves"][-1] - got["ctrl_pts"][s, a]).max() <= TOL_CONTROL
+            o = r["objective"][r["n_curves"] - 1]
+            assert abs(o - got["objective"][s, a]) <= 1e-6 * max(1.0, abs(o))
+    hist_p = np.bincount(got["status"].ravel(), minlength=8)
+    hist_o = np.bincount(ref["status"].ravel(), minlength=8)
+    ok = ~bad & (ref["n_curves"] > 0)
+    print(f"{label}: {S * N * got['status'].shape[-1]} QPs, status histogram product {hist_p.tolist()} oracle(double) {hist_o.tolist()}, "
+          f"{len(redo)} agents re-checked in long double, max control-point error {err[ok].max() if ok.any() else 0.0:.2e}")
+    return ref
+
+
+def closed_loop_snapshot(M, h, st, tg, steps):
+    """The bench's workload: the swarm stepped `steps` control steps by the product itself (bench.py)."""
+    import torch
+    S, N = st.shape[:2]
+    cur, d_tg = torch.tensor(st, device="cuda"), torch.tensor(tg, device="cuda")
+    ctrl = torch.zeros((S, N, h.n), dtype=torch.float64, device="cuda")
+    status = torch.zeros((S, N, 2), dtype=torch.int32, device="cuda")
+    ncv = torch.zeros((S, N), dtype=torch.int32, device="cuda")
+    for _ in range(steps):
+        h.step_batch(S, cur, d_tg, ctrl, status, ncv)
+        h.rollout(S, cur, ctrl, ncv, cur)
+    torch.cuda.synchronize()
+    return cur.cpu().numpy()
+
+
+def inject_infeasible(st, frac, d_min, seed):
+    """`frac` of the agents get |v0| > v_max (the velocity row at k = 0 then contradicts the
+    initial-velocity equality), another `frac` are put inside d_min of a neighbour with closing velocity."""
+    rng = np.random.default_rng(seed)
+    S, N = st.shape[:2]
+    st = st.copy()
+    n = max(1, int(frac * S * N))
+    idx = rng.choice(S * N, size=2 * n, replace=False)
+    for g in idx[:n]:
+        st[g // N, g % N, 3] = 2.0 + rng.uniform(0.05, 1.0)
+    for g in idx[n:]:
+        s, a = g // N, g % N
+        b = (a + 1) % N
+        dirn = rng.normal(size=2)
+        dirn /= np.linalg.norm(dirn)
+        st[s, a, :2] = st[s, b, :2] + dirn * d_min * rng.uniform(0.6, 0.95)
+        st[s, a, 3:5] = -dirn * rng.uniform(0.5, 1.5)   # closing
+    return st
+
+
 def tight_swarm(S, N, seed):
     st, tg = bench.make_swarm(S, N, seed)
     st[:, :, :2] *= 0.8      # neighbours at 0.94 .. 1.9 m with d_min = 0.8: safety rows bind
@@ -78,15 +141,17 @@ def test_north_star_full_size_4096x16(M, O, monkeypatch):
     U = O.get_table(oc, "U_basis")
     du = np.abs(np.einsum("kn,san->sak", U, g2["ctrl_pts"] - got["ctrl_pts"]))[got["n_curves"] > 0].max()
     assert du <= 1e-7, du
-    # oracle on a random sample of the batch
-    rng = np.random.default_rng(5)
-    worst = 0.0
-    for s, a in zip(rng.integers(0, S, 48), rng.integers(0, N, 48)):
-        r = O.optimize(oc, st[s], int(a), np.tile(tg[s, a], cfg.k_hor))
-        assert list(r["status"]) == list(got["status"][s, a])
-        if r["n_curves"]:
-            worst = max(worst, np.abs(r["curves"][-1] - got["ctrl_pts"][s, a]).max())
-    assert worst <= TOL_CONTROL
+    # the oracle on EVERY agent of the batch
+    oracle_all(O, oc, st, tg, got, "4096 x 16 tight swarm")
+    # ... and on the bench's own workload: closed-loop snapshots (safety rows active, some QPs infeasible)
+    # with 1 % infeasible QPs of each kind injected on top
+    st0, tg0 = bench.make_swarm(S, N, 20261104)
+    for steps in (15, 30):
+        snap = closed_loop_snapshot(M, h, st0, tg0, steps)
+        snap = inject_infeasible(snap, 0.01, cfg.d_min, steps)
+        g = h.step_batch_host(snap, tg0)
+        oracle_all(O, oc, snap, tg0, g, f"4096 x 16 closed-loop snapshot after {steps} steps + 1 % injected")
+        assert (g["status"] == M.STATUS_INFEASIBLE).sum() >= 0.01 * S * N
     h.close()
     # the lane-group kernel on the same batch
     monkeypatch.setenv("MPCCBF_LANES", "32")
@@ -117,12 +182,44 @@ def test_dense_swarm_full_size_256_agents(M, O):
     f = feasibility(O, oc, cfg, st, tg, got)
     assert f["n_ok"] >= 0.5 * S * N
     assert f["box"] <= 1e-9 and f["eq"] <= 1e-9 and f["cbf"] <= TOL_CBF_VIOL, f
-    worst = 0.0
-    for s, a in ((0, 0), (3, 119), (7, 255), (5, 136)):
-        r = O.optimize(oc, st[s], a, np.tile(tg[s, a], cfg.k_hor))
-        assert list(r["status"]) == list(got["status"][s, a])
-        if r["n_curves"]:
-            worst = max(worst, np.abs(r["curves"][-1] - got["ctrl_pts"][s, a]).max())
-    assert worst <= TOL_CONTROL
+    oracle_all(O, oc, st, tg, got, "8 x 256 dense swarm")        # every one of the 2048 agents (m = 672 rows each)
+    snap = closed_loop_snapshot(M, h, st, tg, 10)
+    oracle_all(O, oc, snap, tg, h.step_batch_host(snap, tg), "8 x 256 dense swarm, closed-loop snapshot after 10 steps")
     h.close()
-    print(f"8 x 256: {f}, oracle sample error {worst:.2e}")
+    print(f"8 x 256: {f}")
+
+
+@pytest.mark.parametrize("K,N,S", [(40, 64, 6), (10, 64, 12), (40, 32, 12)])
+def test_sweep_corners_against_the_oracle(M, O, K, N, S):
+    # BASELINE configs[4] corners that bench_sweep.py times: horizon 40 (8 pieces, n = 96) and 64-agent swarms
+    p = int(np.ceil((K - 1) * 0.1 / 0.5 - 1e-9))
+    cfg = M.default_config(k_hor=K, num_pieces=p, d_min=0.8, num_agents=N, max_scenarios=S)
+    oc = O.base_config(k_hor=K, num_pieces=p, d_min=0.8, num_agents=N)
+    h = M.Handle(cfg)
+    st, tg = bench.make_swarm(S, N, 100 * K + N)
+    st[:, :, :2] *= N / 16 * 0.55   # ring spacing ~ 1.2 .. 2.3 d_min: safety rows bind
+    tg[:, :, :2] *= N / 16 * 0.55
+    st = inject_infeasible(st, 0.01, cfg.d_min, K + N)
+    got = h.step_batch_host(st, tg)
+    oracle_all(O, oc, st, tg, got, f"sweep corner K={K} N={N}")
+    snap = closed_loop_snapshot(M, h, st, tg, 8)
+    oracle_all(O, oc, snap, tg, h.step_batch_host(snap, tg), f"sweep corner K={K} N={N}, closed loop")
+    h.close()
+
+
+def test_cplex_default_feasibility_tolerance(M, O):
+    # CPLEX's default feasibility tolerance is 1e-6 (qpcpp/src/solvers/CPLEX.cpp:114-126 sets none); the
+    # product defaults to 1e-9. With feas_tol = 1e-6 on both sides statuses and controls must still agree,
+    # and QPs infeasible by less than 1e-6 flip from INFEASIBLE to OPTIMAL.
+    S, N = 512, 16
+    kw = dict(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N)
+    st, tg = tight_swarm(S, N, 77)
+    st[:, 0, 3] = 2.0 + np.linspace(-2e-6, 2e-6, S)   # |v0| straddles v_max = 2 by less than / more than 1e-6
+    res = {}
+    for tol in (1e-6, 1e-9):
+        h = M.Handle(M.default_config(max_scenarios=S, feas_tol=tol, **kw))
+        got = h.step_batch_host(st, tg)
+        oracle_all(O, O.base_config(feas_tol=tol, **kw), st, tg, got, f"feas_tol {tol:g}", feas_tol=tol)
+        res[tol] = got["status"][:, 0, 0].copy()
+        h.close()
+    assert (res[1e-6] != res[1e-9]).any() and ((res[1e-6] == M.STATUS_OPTIMAL) >= (res[1e-9] == M.STATUS_OPTIMAL)).all()
