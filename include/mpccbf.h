@@ -46,9 +46,11 @@ extern "C" {
 #define MPCCBF_STATUS_SKIPPED 7
 
 /* Which solver the controller path uses. */
-#define MPCCBF_SOLVER_AUTO 0     /* reduced when the structure allows, else dense ADMM     */
-#define MPCCBF_SOLVER_REDUCED 1  /* fused null-space active-set kernel (C^3 cubic pieces)   */
-#define MPCCBF_SOLVER_DENSE 2    /* full-space assembly + one-CTA-per-QP ADMM/OSQP kernel   */
+#define MPCCBF_SOLVER_AUTO 0     /* reduced when the structure allows, else dense           */
+#define MPCCBF_SOLVER_REDUCED 1  /* fused null-space active-set kernel (C^3 cubic pieces),  */
+                                 /* with or without slack_mode                              */
+#define MPCCBF_SOLVER_DENSE 2    /* the configuration does not reduce: only the S-qp seam   */
+                                 /* (mpccbf_solve_qp_dense, ADMM/OSQP kernel) is available  */
 
 /* Configuration: union of the reference's parameter structs
  *   mpc::PiecewiseBezierParams / MPCParams / TuningParams / PhysicalLimits
@@ -74,9 +76,9 @@ typedef struct mpccbf_config {
     double cbf_gamma;         /* 5.0 in the reference                                   */
     int32_t impc_iter;        /* cbf_params.impc_iter                                   */
     int32_t slack_mode;       /* cbf_params.slack_mode: one slack >= 0 per neighbour on its
-                               * safety rows (ConnectivityIMPCCBF.cpp:76-100); controller
-                               * entries then run assemble -> ADMM kernel -> finish on the
-                               * device (num_agents - 1 <= 122), see DESIGN.md section 8      */
+                               * safety rows (ConnectivityIMPCCBF.cpp:76-100), solved inside
+                               * the fused active-set kernel with per-neighbour multiplier
+                               * caps (no limit on num_agents), see DESIGN.md section 8       */
     double slack_cost;        /* cbf_params.slack_cost                                  */
     double slack_decay;       /* cbf_params.slack_decay_rate                            */
     int32_t num_agents;       /* robots per scenario (tasks.so length)                  */
@@ -120,10 +122,9 @@ const char* mpccbf_version(void);
 /* Decision-vector length n = num_pieces*3*num_ctrl_pts, layout x[piece*3c + axis*c + cp]
  * (BezierQPOperations.cpp:37, PiecewiseBezierMPCQPGenerator.cpp:9-34). */
 int32_t mpccbf_num_decision_vars(const mpccbf_handle* h);
-/* Which solver the controller path resolved to: MPCCBF_SOLVER_REDUCED (fused active-set kernels) or
- * MPCCBF_SOLVER_DENSE (ADMM kernel: slack mode on the reduced QPs; for configurations that do not
- * reduce at all only mpccbf_solve_qp_dense is available and the controller entries return
- * MPCCBF_ERR_UNSUPPORTED). */
+/* Which solver the controller path resolved to: MPCCBF_SOLVER_REDUCED (fused active-set kernels, also in
+ * slack mode) or MPCCBF_SOLVER_DENSE (the configuration does not reduce: only mpccbf_solve_qp_dense is
+ * available and the controller entries return MPCCBF_ERR_UNSUPPORTED). */
 int32_t mpccbf_active_solver(const mpccbf_handle* h);
 
 /* Batched control step == ConnectivityIMPCCBF::optimize for every agent of every scenario
@@ -155,6 +156,32 @@ int mpccbf_step_batch_host_async(mpccbf_handle* h, int32_t num_scenarios, const 
                                  const double* targets, double* ctrl_pts, int32_t* status,
                                  int32_t* n_curves, double* objective);
 int mpccbf_synchronize(mpccbf_handle* h);
+
+/* ---- Compact result form ------------------------------------------------------------------------------
+ * With C^3 cubic pieces the n control points of a curve are an exact linear image of the agent's own
+ * state and 6 numbers: x[piece, axis, cp] = Y [pos; vel] + W v, v = the whitened free dof (2 per axis).
+ * These entries return v_free [S][N][6] (zeros where n_curves == 0) instead of ctrl_pts [S][N][n]: 48
+ * instead of 8 n bytes per agent cross PCIe, which is what bounds the host-pointer calls. The caller of
+ * ConnectivityIMPCCBF::optimize only evaluates trajs.back() at h / Ts sub-steps
+ * (MPCCBFFormationControl_example.cpp:191-205): mpccbf_eval_compact does that straight from (state, v),
+ * mpccbf_expand_ctrl_pts rebuilds the control points (bit-identical to mpccbf_step_batch's) on the host.
+ * Only for handles whose solver is MPCCBF_SOLVER_REDUCED. */
+int mpccbf_step_batch_compact(mpccbf_handle* h, int32_t num_scenarios, const double* states,
+                              const double* targets, double* v_free, int32_t* status, int32_t* n_curves,
+                              double* objective, void* cuda_stream);                 /* device pointers */
+int mpccbf_step_batch_host_compact(mpccbf_handle* h, int32_t num_scenarios, const double* states,
+                                   const double* targets, double* v_free, int32_t* status,
+                                   int32_t* n_curves, double* objective);            /* host pointers   */
+int mpccbf_step_batch_host_compact_async(mpccbf_handle* h, int32_t num_scenarios, const double* states,
+                                         const double* targets, double* v_free, int32_t* status,
+                                         int32_t* n_curves, double* objective);
+/* Host only. states [count][6], v_free [count][6], n_curves [count] or NULL, ctrl_pts [count][n]. */
+int mpccbf_expand_ctrl_pts(const mpccbf_handle* h, int64_t count, const double* states,
+                           const double* v_free, const int32_t* n_curves, double* ctrl_pts);
+/* Host only. out [count][3] = deriv-th derivative of every agent's curve at time t, with the piece lookup
+ * and clamping of SingleParameterPiecewiseCurve::eval (splines/src/curves/SingleParameterPiecewiseCurve.cpp:94-127). */
+int mpccbf_eval_compact(const mpccbf_handle* h, int64_t count, const double* states, const double* v_free,
+                        double t, int32_t deriv, double* out);
 
 /* Single-agent drop-in for S-ctl (host pointers): states [N][6], ref [3*k_hor] (only used as a
  * per-step reference: ref[3k..3k+2] is the target at horizon step k), ctrl_pts [impc_iter][n]
@@ -307,11 +334,9 @@ int mpccbf_linear_cost(const mpccbf_handle* h, const double* x0, const double* r
 void* mpccbf_host_alloc(size_t bytes);
 void mpccbf_host_free(void* p);
 
-/* Slack mode runs in two tiers: the fused hard-row kernels first, then a per-agent KKT check of whether
- * that optimum is also the slack-mode optimum (every safety multiplier within its weight); agents that
- * fail the check - hard QP infeasible, a cap exceeded, degenerate active set - are re-solved with the
- * slack variables by the ADMM kernel. Returns the cumulative number of agent-steps that took the second
- * tier on this handle (-1 for a NULL handle). */
+/* Round 1 solved slack-mode QPs in two tiers and reported here how many agent-steps took the second (ADMM)
+ * one. The slack caps now live in the active-set kernel: always 0 (-1 for a NULL handle). Kept so that
+ * callers built against the round-1 header keep linking. */
 int64_t mpccbf_slack_fallback_count(const mpccbf_handle* h);
 
 /* Counters since create (may be NULL individually). */

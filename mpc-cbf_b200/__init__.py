@@ -34,6 +34,8 @@ EXPORTED_SYMBOLS = [
     "mpccbf_linear_cost", "mpccbf_get_counters", "mpccbf_host_alloc", "mpccbf_host_free",
     "mpccbf_cbf_filter_batch", "mpccbf_cbf_filter_batch_host", "mpccbf_conn_rows", "mpccbf_run_episode",
     "mpccbf_run_episode_ex", "mpccbf_step_batch_host_async", "mpccbf_synchronize", "mpccbf_slack_fallback_count",
+    "mpccbf_step_batch_compact", "mpccbf_step_batch_host_compact", "mpccbf_step_batch_host_compact_async",
+    "mpccbf_expand_ctrl_pts", "mpccbf_eval_compact",
 ]
 
 
@@ -127,6 +129,11 @@ def lib(path=None):
     L.mpccbf_step_batch_host.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
     L.mpccbf_step_batch_host_async.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
     L.mpccbf_synchronize.argtypes = [vp]
+    L.mpccbf_step_batch_compact.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, vp]
+    L.mpccbf_step_batch_host_compact.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+    L.mpccbf_step_batch_host_compact_async.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+    L.mpccbf_expand_ctrl_pts.argtypes = [vp, i64, vp, vp, vp, vp]
+    L.mpccbf_eval_compact.argtypes = [vp, i64, vp, vp, dbl, i32, vp]
     L.mpccbf_step_agents.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
     L.mpccbf_optimize_one.argtypes = [vp, vp, i32, vp, vp, vp, vp]
     L.mpccbf_solve_qp_dense.argtypes = [vp, i32, i32, i32] + [vp] * 11
@@ -267,6 +274,46 @@ class Handle:
 
     def synchronize(self):
         self._check(self._L.mpccbf_synchronize(self._h))
+
+    # ---- compact result form: v_free [S][N][6] instead of ctrl_pts [S][N][n] ---------------------
+    def step_batch_host_compact(self, states, targets, out=None):
+        states, targets = _f64(states), _f64(targets)
+        S, N = states.shape[0], states.shape[1]
+        it = self.cfg.impc_iter
+        if out is None:
+            out = dict(v_free=np.zeros((S, N, 6)), status=np.zeros((S, N, it), dtype=np.int32),
+                       n_curves=np.zeros((S, N), dtype=np.int32), objective=np.zeros((S, N)))
+        self._check(self._L.mpccbf_step_batch_host_compact(self._h, S, states.ctypes.data, targets.ctypes.data,
+                                                           _ptr(out["v_free"]), _ptr(out["status"]),
+                                                           _ptr(out["n_curves"]), _ptr(out["objective"])))
+        return out
+
+    def step_batch_host_compact_async(self, states, targets, out):
+        S = states.shape[0]
+        self._check(self._L.mpccbf_step_batch_host_compact_async(self._h, S, states.ctypes.data, targets.ctypes.data,
+                                                                 _ptr(out["v_free"]), _ptr(out["status"]),
+                                                                 _ptr(out["n_curves"]), _ptr(out["objective"])))
+
+    def step_batch_compact(self, S, states, targets, v_free, status, n_curves=None, objective=None, stream=None):
+        """Device pointers (torch tensors or ints), asynchronous on `stream`."""
+        self._check(self._L.mpccbf_step_batch_compact(self._h, S, _ptr(states), _ptr(targets), _ptr(v_free), _ptr(status),
+                                                      _ptr(n_curves), _ptr(objective), stream))
+
+    def expand_ctrl_pts(self, states, v_free, n_curves=None):
+        states, v_free = _f64(states).reshape(-1, 6), _f64(v_free).reshape(-1, 6)
+        cnt = states.shape[0]
+        nc = np.ascontiguousarray(n_curves, dtype=np.int32).ravel() if n_curves is not None else None
+        out = np.zeros((cnt, self.n))
+        self._check(self._L.mpccbf_expand_ctrl_pts(self._h, cnt, states.ctypes.data, v_free.ctypes.data,
+                                                   nc.ctypes.data if nc is not None else None, out.ctypes.data))
+        return out
+
+    def eval_compact(self, states, v_free, t, deriv=0):
+        states, v_free = _f64(states).reshape(-1, 6), _f64(v_free).reshape(-1, 6)
+        out = np.zeros((states.shape[0], 3))
+        self._check(self._L.mpccbf_eval_compact(self._h, states.shape[0], states.ctypes.data, v_free.ctypes.data,
+                                                float(t), int(deriv), out.ctypes.data))
+        return out
 
     def cbf_filter_batch_host(self, states, desired_u):
         """cbf::ConnectivityControl::optimize for every agent: dict(u [S][N][3], status [S][N], lambda2 [S])."""

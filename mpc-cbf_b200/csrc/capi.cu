@@ -3,6 +3,7 @@
 // returns MPCCBF_ERR_CUDA.
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -242,7 +243,7 @@ int build_device_tables(mpccbf_handle* h) {
 }
 
 int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_count, const double* states,
-             const double* targets, int ref_mode, double* ctrl, double* ctrl_all, int32_t* status,
+             const double* targets, int ref_mode, double* ctrl, double* ctrl_all, double* v_out, int32_t* status,
              int32_t* n_curves, double* objective, int32_t* iters, cudaStream_t stream) {
     if (h->solver != MPCCBF_SOLVER_REDUCED) {
         set_error("controller path: this configuration does not reduce to the 6-dof form (needs cubic pieces with "
@@ -254,6 +255,7 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
     a.targets = targets;
     a.ctrl_pts = ctrl;
     a.ctrl_all = ctrl_all;
+    a.v_out = v_out;
     a.status = status;
     a.n_curves = n_curves;
     a.objective = objective;
@@ -451,7 +453,7 @@ int mpccbf_step_agents(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t
         return MPCCBF_ERR_INVALID;
     }
     CUDA_TRY(cudaSetDevice(h->device));
-    return run_step(h, S, agent_begin, agent_count, states, targets, 0, ctrl_pts, nullptr, status, n_curves,
+    return run_step(h, S, agent_begin, agent_count, states, targets, 0, ctrl_pts, nullptr, nullptr, status, n_curves,
                     objective, h->w_iters, static_cast<cudaStream_t>(cuda_stream));
 }
 
@@ -491,11 +493,11 @@ int mpccbf_synchronize(mpccbf_handle* h) {
 }
 
 static int step_host_enqueue(mpccbf_handle* h, int32_t S, const double* states, const double* targets, double* ctrl_pts,
-                             int32_t* status, int32_t* n_curves, double* objective, bool zero_copy);
+                             int32_t* status, int32_t* n_curves, double* objective, bool zero_copy, bool compact);
 
 int mpccbf_step_batch_host(mpccbf_handle* h, int32_t S, const double* states, const double* targets,
                            double* ctrl_pts, int32_t* status, int32_t* n_curves, double* objective) {
-    const int rc = step_host_enqueue(h, S, states, targets, ctrl_pts, status, n_curves, objective, true);
+    const int rc = step_host_enqueue(h, S, states, targets, ctrl_pts, status, n_curves, objective, true, false);
     if (rc != MPCCBF_OK || S == 0) return rc;
     return mpccbf_synchronize(h);
 }
@@ -506,11 +508,111 @@ int mpccbf_step_batch_host(mpccbf_handle* h, int32_t S, const double* states, co
 // with the other handle's solve (0.55 ms per batch, the PCIe bound for 31 MB).
 int mpccbf_step_batch_host_async(mpccbf_handle* h, int32_t S, const double* states, const double* targets,
                                  double* ctrl_pts, int32_t* status, int32_t* n_curves, double* objective) {
-    return step_host_enqueue(h, S, states, targets, ctrl_pts, status, n_curves, objective, false);
+    return step_host_enqueue(h, S, states, targets, ctrl_pts, status, n_curves, objective, false, false);
 }
 
+int mpccbf_step_batch_compact(mpccbf_handle* h, int32_t S, const double* states, const double* targets, double* v_free,
+                              int32_t* status, int32_t* n_curves, double* objective, void* cuda_stream) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (S < 0 || S > h->cfg.max_scenarios || !states || !targets || !v_free || !status) {
+        set_error("mpccbf_step_batch_compact: invalid argument (num_scenarios must be <= max_scenarios)");
+        return MPCCBF_ERR_INVALID;
+    }
+    CUDA_TRY(cudaSetDevice(h->device));
+    return run_step(h, S, 0, h->cfg.num_agents, states, targets, 0, nullptr, nullptr, v_free, status, n_curves, objective,
+                    h->w_iters, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mpccbf_step_batch_host_compact(mpccbf_handle* h, int32_t S, const double* states, const double* targets, double* v_free,
+                                   int32_t* status, int32_t* n_curves, double* objective) {
+    const int rc = step_host_enqueue(h, S, states, targets, v_free, status, n_curves, objective, false, true);
+    if (rc != MPCCBF_OK || S == 0) return rc;
+    return mpccbf_synchronize(h);
+}
+
+int mpccbf_step_batch_host_compact_async(mpccbf_handle* h, int32_t S, const double* states, const double* targets,
+                                         double* v_free, int32_t* status, int32_t* n_curves, double* objective) {
+    return step_host_enqueue(h, S, states, targets, v_free, status, n_curves, objective, false, true);
+}
+
+// x[piece, axis, cp] = Y1 [pos; vel] + W1 [va; vb] per axis: the exact linear map the kernels apply on the device
+int mpccbf_expand_ctrl_pts(const mpccbf_handle* h, int64_t count, const double* states, const double* v_free,
+                           const int32_t* n_curves, double* ctrl_pts) {
+    if (!h || count < 0 || !states || !v_free || !ctrl_pts) {
+        set_error("mpccbf_expand_ctrl_pts: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (h->solver != MPCCBF_SOLVER_REDUCED) {
+        set_error("mpccbf_expand_ctrl_pts: the configuration has no reduced form");
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    const int n = h->tab.n, c = h->tab.c, m1 = h->tab.m1;
+    const double* yw = h->h_yw.data();
+    for (int64_t g = 0; g < count; ++g) {
+        const double* s = states + g * 6;
+        const double* v = v_free + g * 6;
+        double* out = ctrl_pts + g * n;
+        if (n_curves && n_curves[g] <= 0) {
+            for (int i = 0; i < n; ++i) out[i] = 0.0;
+            continue;
+        }
+        for (int j = 0; j < m1; ++j) {
+            const int piece = j / c, cp = j - piece * c;
+            const double* y = yw + 4 * j;
+            for (int ax = 0; ax < 3; ++ax)
+                out[piece * 3 * c + ax * c + cp] = std::fma(y[0], s[ax], std::fma(y[1], s[3 + ax], std::fma(y[2], v[2 * ax], y[3] * v[2 * ax + 1])));
+        }
+    }
+    return MPCCBF_OK;
+}
+
+// curve^(deriv)(t) straight from the compact record: piece lookup and clamping of
+// SingleParameterPiecewiseCurve::eval (splines/src/curves/SingleParameterPiecewiseCurve.cpp:94-127)
+int mpccbf_eval_compact(const mpccbf_handle* h, int64_t count, const double* states, const double* v_free, double t,
+                        int32_t deriv, double* out) {
+    if (!h || count < 0 || !states || !v_free || !out || deriv < 0 || t < 0) {
+        set_error("mpccbf_eval_compact: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (h->solver != MPCCBF_SOLVER_REDUCED || h->tab.c > 8) {
+        set_error("mpccbf_eval_compact: the configuration has no reduced form");
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    const int c = h->tab.c, p = h->tab.p;
+    const double T = h->cfg.piece_max_param;
+    double cum = 0.0, prev = 0.0;
+    int piece = p - 1;
+    for (int i = 0; i < p; ++i) {  // first piece whose cumulative end >= t (lower_bound)
+        prev = cum;
+        cum += T;
+        if (!(cum < t)) {
+            piece = i;
+            break;
+        }
+    }
+    if (t > cum) {
+        set_error("mpccbf_eval_compact: parameter beyond the curve's max_parameter");
+        return MPCCBF_ERR_INVALID;
+    }
+    const double local = std::min(T, std::max(0.0, t - prev));
+    xreal basis[8];
+    bernstein_deriv(c, T, local, deriv, basis);
+    double r[4] = {0, 0, 0, 0};  // basis' [Y1 | W1] of this piece
+    for (int cp = 0; cp < c; ++cp)
+        for (int k = 0; k < 4; ++k) r[k] += static_cast<double>(basis[cp]) * h->h_yw[4 * (piece * c + cp) + k];
+    for (int64_t g = 0; g < count; ++g) {
+        const double* s = states + g * 6;
+        const double* v = v_free + g * 6;
+        for (int ax = 0; ax < 3; ++ax) out[g * 3 + ax] = r[0] * s[ax] + r[1] * s[3 + ax] + r[2] * v[2 * ax] + r[3] * v[2 * ax + 1];
+    }
+    return MPCCBF_OK;
+}
+
+// compact: `ctrl_pts` receives [S][N][6] whitened free dof instead of [S][N][n] control points (48 instead of 8 n
+// bytes per agent over PCIe)
 static int step_host_enqueue(mpccbf_handle* h, int32_t S, const double* states, const double* targets, double* ctrl_pts,
-                             int32_t* status, int32_t* n_curves, double* objective, bool zero_copy) {
+                             int32_t* status, int32_t* n_curves, double* objective, bool zero_copy, bool compact) {
     int rc = require_device(h);
     if (rc != MPCCBF_OK) return rc;
     if (S < 0 || S > h->cfg.max_scenarios || !states || !targets || !ctrl_pts || !status) {
@@ -519,7 +621,7 @@ static int step_host_enqueue(mpccbf_handle* h, int32_t S, const double* states, 
     }
     if (S == 0) return MPCCBF_OK;
     CUDA_TRY(cudaSetDevice(h->device));
-    const size_t N = h->cfg.num_agents, n = h->tab.n, it = h->cfg.impc_iter;
+    const size_t N = h->cfg.num_agents, n = compact ? 6 : h->tab.n, it = h->cfg.impc_iter;
     // Control points are 384 of the 404 output bytes per agent. When the caller's ctrl_pts buffer is
     // pinned host memory (mpccbf_host_alloc, cudaHostAlloc / cudaHostRegister: mapped under UVA) the
     // kernel stores them straight into it — coalesced posted writes over PCIe that overlap the solve —
@@ -562,8 +664,8 @@ static int step_host_enqueue(mpccbf_handle* h, int32_t S, const double* states, 
         }
         double* ctrl_out = ctrl_dev ? ctrl_dev + a0 * n : h->w_ctrl + a0 * n;
         rc = run_step(h, s1 - s0, 0, h->cfg.num_agents, states_dev ? states_dev + a0 * 6 : h->w_states + a0 * 6,
-                      states_dev ? targets_dev + a0 * 3 : h->w_targets + a0 * 3, 0, ctrl_out,
-                      nullptr, h->w_status + a0 * it, h->w_ncurves + a0, h->w_obj + a0, h->w_iters + a0 * it, st);
+                      states_dev ? targets_dev + a0 * 3 : h->w_targets + a0 * 3, 0, compact ? nullptr : ctrl_out,
+                      nullptr, compact ? ctrl_out : nullptr, h->w_status + a0 * it, h->w_ncurves + a0, h->w_obj + a0, h->w_iters + a0 * it, st);
         if (rc != MPCCBF_OK) return rc;
         if (!ctrl_dev)
             CUDA_TRY(cudaMemcpyAsync(ctrl_pts + a0 * n, h->w_ctrl + a0 * n, sizeof(double) * cnt * n, cudaMemcpyDeviceToHost, st));
@@ -590,7 +692,7 @@ int mpccbf_optimize_one(mpccbf_handle* h, const double* states, int32_t self_idx
     int32_t* d_status = h->o_status;
     int32_t* d_nc = h->o_status + it;
     int32_t* d_iters = h->o_status + it + 1;
-    rc = run_step(h, 1, self_idx, 1, h->o_states, h->o_ref, 1, h->o_ctrl, h->o_all, d_status, d_nc, nullptr, d_iters, st);
+    rc = run_step(h, 1, self_idx, 1, h->o_states, h->o_ref, 1, h->o_ctrl, h->o_all, nullptr, d_status, d_nc, nullptr, d_iters, st);
     if (rc != MPCCBF_OK) return rc;
     std::vector<int32_t> hs(it + 1);
     CUDA_TRY(cudaMemcpyAsync(hs.data(), d_status, sizeof(int32_t) * (it + 1), cudaMemcpyDeviceToHost, st));
@@ -766,7 +868,7 @@ int mpccbf_run_episode_ex(mpccbf_handle* h, int32_t S, double* states, const dou
     for (int step = 0; step < steps; ++step) {
         a.step = step;
         if (opts->order == MPCCBF_ORDER_JACOBI) {
-            rc = run_step(h, S, 0, N, states, targets, 0, h->e_ctrl, nullptr, h->e_status, h->e_nc, nullptr, h->w_iters, st);
+            rc = run_step(h, S, 0, N, states, targets, 0, h->e_ctrl, nullptr, nullptr, h->e_status, h->e_nc, nullptr, h->w_iters, st);
             if (rc != MPCCBF_OK) return rc;
             a.agent_begin = 0; a.agent_count = N; a.do_metrics = 1;
             CUDA_TRY(launch_episode_advance(a, h->sm_count, st));
@@ -774,7 +876,7 @@ int mpccbf_run_episode_ex(mpccbf_handle* h, int32_t S, double* states, const dou
         } else {
             for (int ag = 0; ag < N; ++ag) {
                 CUDA_TRY(launch_gather_agent_targets(S, N, ag, targets, h->e_tg, st));
-                rc = run_step(h, S, ag, 1, states, h->e_tg, 0, h->e_ctrl, nullptr, h->e_status, h->e_nc, nullptr, h->w_iters, st);
+                rc = run_step(h, S, ag, 1, states, h->e_tg, 0, h->e_ctrl, nullptr, nullptr, h->e_status, h->e_nc, nullptr, h->w_iters, st);
                 if (rc != MPCCBF_OK) return rc;
                 a.agent_begin = ag; a.agent_count = 1; a.do_metrics = (ag == N - 1) ? 1 : 0;
                 CUDA_TRY(launch_episode_advance(a, h->sm_count, st));
@@ -884,7 +986,7 @@ int mpccbf_get_counters(const mpccbf_handle* h, int64_t* kernel_launches, int64_
 // host for CPU-only CI. NOT part of include/mpccbf.h and NOT compiled into libmpccbf.so.
 int mpccbf_emul_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_count, int32_t ref_mode,
                      const double* states, const double* targets, double* ctrl_pts, double* ctrl_all,
-                     int32_t* status, int32_t* n_curves, double* objective, int32_t* iters) {
+                     int32_t* status, int32_t* n_curves, double* objective, int32_t* iters, double* v_out) {
     if (!h || h->has_device || h->solver != MPCCBF_SOLVER_REDUCED) {
         set_error("mpccbf_emul_step: needs a host-only (device = -1) reducible handle");
         return MPCCBF_ERR_INVALID;
@@ -898,6 +1000,7 @@ int mpccbf_emul_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t a
     a.n_curves = n_curves;
     a.objective = objective;
     a.gi_iters = iters;
+    a.v_out = v_out;
     a.num_qp = S * agent_count;
     a.agent_begin = agent_begin;
     a.agent_count = agent_count;

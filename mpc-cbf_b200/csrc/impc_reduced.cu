@@ -456,19 +456,15 @@ __host__ __device__ void impc_agent(const DevTables& T, const StepArgs& a, int g
         ++n_ok;
 #pragma unroll
         for (int i = 0; i < R; ++i) vlast[i] = v[i];
-        if (a.v_all && gl == 0) {
-#pragma unroll
-            for (int i = 0; i < R; ++i) a.v_all[(static_cast<size_t>(g) * T.iters + it) * R + i] = v[i];
-        }
         if (a.ctrl_all) {
             double* out = a.ctrl_all + (static_cast<size_t>(g) * T.iters + it) * T.n;
             for (int i = gl; i < T.n; i += W) {
                 const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
                 const int ax = rem / T.c, cp = rem - ax * T.c;
                 const double* y = yw + (piece * T.c + cp) * 4;
-                out[i] = y[0] * sel3(ax, qp.s[0][0], qp.s[1][0], qp.s[2][0]) +
-                         y[1] * sel3(ax, qp.s[0][1], qp.s[1][1], qp.s[2][1]) +
-                         y[2] * sel3(ax, v[0], v[2], v[4]) + y[3] * sel3(ax, v[1], v[3], v[5]);
+                out[i] = fma(y[0], sel3(ax, qp.s[0][0], qp.s[1][0], qp.s[2][0]),
+                             fma(y[1], sel3(ax, qp.s[0][1], qp.s[1][1], qp.s[2][1]),
+                                 fma(y[2], sel3(ax, v[0], v[2], v[4]), y[3] * sel3(ax, v[1], v[3], v[5]))));
             }
         }
         if (it + 1 < T.iters) {
@@ -487,17 +483,20 @@ __host__ __device__ void impc_agent(const DevTables& T, const StepArgs& a, int g
     }
     // ---- outputs --------------------------------------------------------------------------
     {
+        if (a.v_out && gl == 0) {
+#pragma unroll
+            for (int i = 0; i < R; ++i) a.v_out[static_cast<size_t>(g) * R + i] = (n_ok > 0) ? vlast[i] : 0.0;
+        }
         double* out = a.ctrl_pts + static_cast<size_t>(g) * T.n;
-        for (int i = gl; i < T.n; i += W) {
+        for (int i = gl; a.ctrl_pts && i < T.n; i += W) {
             double val = 0.0;
             if (n_ok > 0) {
                 const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
                 const int ax = rem / T.c, cp = rem - ax * T.c;
                 const double* y = yw + (piece * T.c + cp) * 4;
-                val = y[0] * sel3(ax, qp.s[0][0], qp.s[1][0], qp.s[2][0]) +
-                      y[1] * sel3(ax, qp.s[0][1], qp.s[1][1], qp.s[2][1]) +
-                      y[2] * sel3(ax, vlast[0], vlast[2], vlast[4]) +
-                      y[3] * sel3(ax, vlast[1], vlast[3], vlast[5]);
+                val = fma(y[0], sel3(ax, qp.s[0][0], qp.s[1][0], qp.s[2][0]),
+                          fma(y[1], sel3(ax, qp.s[0][1], qp.s[1][1], qp.s[2][1]),
+                              fma(y[2], sel3(ax, vlast[0], vlast[2], vlast[4]), y[3] * sel3(ax, vlast[1], vlast[3], vlast[5]))));
             }
             out[i] = val;
         }

@@ -445,7 +445,8 @@ MPCCBF_HD void build_candidates(RowsXY<SOFT>& rx, const DevTables& T, unsigned s
 
 MPCCBF_HD double ctrl_point(const double* y, int ax, const double* sol) {
     // x[piece, ax, cp] = Y1 (pos, vel) + W1 (va, vb)
-    return y[0] * sol[ax] + y[1] * sol[3 + ax] + y[2] * sol[6 + 2 * ax] + y[3] * sol[7 + 2 * ax];
+    // (explicit fma chain: mpccbf_expand_ctrl_pts evaluates the same expression on the host, bit for bit)
+    return fma(y[0], sol[ax], fma(y[1], sol[3 + ax], fma(y[2], sol[6 + 2 * ax], y[3] * sol[7 + 2 * ax])));
 }
 
 // Everything optimize() does for agent-QP g (one thread).
@@ -649,11 +650,6 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         vlast[4] = gy.v[0];
         vlast[5] = gy.v[1];
         if constexpr (SOFT) pen_last = (run && a.objective) ? rx.penalty(gx.v) : 0.0;
-        if (a.v_all) {  // slack-mode verification reads the iterates in whitened coordinates
-            double* vo = a.v_all + (sbase + it) * 6;
-#pragma unroll
-            for (int i = 0; i < 6; ++i) vo[i] = vlast[i];
-        }
         if (a.ctrl_all) {  // every iterate (mpccbf_optimize_one): small batches, direct stores
 #pragma unroll
             for (int ax = 0; ax < 3; ++ax) {
@@ -807,7 +803,15 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
             agent_thread<SOFT>(T, a, g, self, c);
         }
         __syncwarp();
-        {   // control points of the last successful iterate: coalesced stores, whole warp
+        if (a.v_out) {  // compact result: the 6 whitened free dof per agent, coalesced
+            double* vo = a.v_out + static_cast<size_t>(g0) * 6;
+            for (int idx = lane; idx < cnt * 6; idx += 32) {
+                const int ag = idx / 6, i = idx - ag * 6;
+                const double* rec = wsol + ag * kSolStride;
+                vo[idx] = (rec[12] > 0.0) ? rec[6 + i] : 0.0;
+            }
+        }
+        if (a.ctrl_pts) {   // control points of the last successful iterate: coalesced stores, whole warp
             double* out = a.ctrl_pts + static_cast<size_t>(g0) * n;
             const int total = cnt * n;
             for (int idx = lane; idx < total; idx += 32) {
@@ -848,8 +852,10 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
             agent_thread<true>(T, a, g, self, c);
         else
             agent_thread<false>(T, a, g, self, c);
+        if (a.v_out)
+            for (int i = 0; i < 6; ++i) a.v_out[static_cast<size_t>(g) * 6 + i] = (sol[12] > 0.0) ? sol[6 + i] : 0.0;
         double* out = a.ctrl_pts + static_cast<size_t>(g) * T.n;
-        for (int i = 0; i < T.n; ++i) {
+        for (int i = 0; a.ctrl_pts && i < T.n; ++i) {
             const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
             const int ax = rem / T.c, cp = rem - ax * T.c;
             out[i] = (sol[12] > 0.0) ? ctrl_point(T.yw + (piece * T.c + cp) * 4, ax, sol.data()) : 0.0;

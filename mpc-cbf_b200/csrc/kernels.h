@@ -15,9 +15,10 @@ namespace mpccbf {
 struct StepArgs {
     const double* states;    // [S][N][6]  full snapshot of every scenario
     const double* targets;   // [B][3]  (ref_mode 0)  or  [B][3K] (ref_mode 1)
-    double* ctrl_pts;        // [B][n]            last successful iterate (zeros if none)
+    double* ctrl_pts;        // [B][n]            last successful iterate (zeros if none); NULL: not wanted
     double* ctrl_all;        // [B][iters][n]     every successful iterate, may be NULL
-    double* v_all = nullptr; // [B][iters][6]     whitened free dof of every successful iterate, may be NULL
+    double* v_out = nullptr; // [B][6]            compact result: whitened free dof of the last successful iterate
+                             //                   (zeros if none); x = Y [pos; vel] + W v. May be NULL
     int32_t* status;         // [B][iters]
     int32_t* n_curves;       // [B]   may be NULL
     double* objective;       // [B]   may be NULL

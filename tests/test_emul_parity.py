@@ -18,7 +18,7 @@ def emul(M):
     d = os.path.join(ROOT, "tests", "emul")
     subprocess.run(["make", "-C", d], check=True, stdout=subprocess.DEVNULL)
     L = M.lib(os.path.join(d, "libmpccbf_emul.so"))
-    L.mpccbf_emul_step.argtypes = [C.c_void_p] + [C.c_int32] * 4 + [C.c_void_p] * 8
+    L.mpccbf_emul_step.argtypes = [C.c_void_p] + [C.c_int32] * 4 + [C.c_void_p] * 9
     return L
 
 
@@ -29,14 +29,17 @@ def run_emul(M, L, cfg, states, targets):
     S, N = states.shape[:2]
     it = cfg.impc_iter
     out = dict(ctrl_pts=np.zeros((S, N, h.n)), status=np.zeros((S, N, it), np.int32),
-               n_curves=np.zeros((S, N), np.int32), objective=np.zeros((S, N)))
+               n_curves=np.zeros((S, N), np.int32), objective=np.zeros((S, N)), v_free=np.zeros((S, N, 6)))
     iters = np.zeros((S, N, it), np.int32)
     st, tg = np.ascontiguousarray(states), np.ascontiguousarray(targets)
     rc = L.mpccbf_emul_step(h._h, S, 0, N, 0, st.ctypes.data, tg.ctypes.data, out["ctrl_pts"].ctypes.data, None,
                             out["status"].ctypes.data, out["n_curves"].ctypes.data, out["objective"].ctypes.data,
-                            iters.ctypes.data)
+                            iters.ctypes.data, out["v_free"].ctypes.data)
     assert rc == 0
     out["iters"] = iters
+    # compact result form: the host-side expansion reproduces the kernel's control points bit for bit, and
+    # evaluating the curve from the compact record equals evaluating the expanded curve
+    assert np.array_equal(h.expand_ctrl_pts(st, out["v_free"], out["n_curves"]).reshape(S, N, -1), out["ctrl_pts"])
     h.close()
     return out
 
@@ -130,3 +133,22 @@ def test_slack_mode_capped_multipliers(M, O, emul, extra, N, S, spread):
     check_step(O, oc, O.get_table(oc, "U_basis"), st, tg, got, check_viol_max=0)
     assert list(got["status"][0, 1]) == [M.STATUS_INFEASIBLE] + [M.STATUS_SKIPPED] * (cfg.impc_iter - 1)
     assert (got["status"] == M.STATUS_OPTIMAL).mean() > 0.95
+
+
+def test_compact_record_evaluates_like_the_expanded_curve(M, O, emul):
+    # mpccbf_eval_compact == SingleParameterPiecewiseCurve::eval of the expanded control points, at the driver's
+    # sub-step times and across piece boundaries (lower_bound piece lookup, clamped local parameter)
+    cfg = M.default_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=8)
+    oc = O.base_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=8)
+    st, tg = swarm(3, 8, seed=5)
+    got = run_emul(M, emul, cfg, st, tg)
+    h = M.Handle(cfg.copy(device=-1), library=emul)
+    for t in (0.0, 0.01, 0.1, 0.5, 0.5000001, 0.99, 1.0, 1.7, 2.0):
+        for d in (0, 1, 2):
+            val = h.eval_compact(st, got["v_free"], t, d).reshape(3, 8, 3)
+            for s in range(3):
+                for a in range(8):
+                    assert np.abs(val[s, a] - O.eval_curve(oc, got["ctrl_pts"][s, a], t, d)).max() <= 1e-9
+    with pytest.raises(M.MpcCbfError):
+        h.eval_compact(st, got["v_free"], 2.1)
+    h.close()

@@ -158,3 +158,28 @@ def test_one_sided_limits_and_single_agent(M, O, torch_cuda):
     check_step(O, oc, O.get_table(oc, "U_basis"), st, tg, got)
     assert (got["status"] == 0).all()
     h.close()
+
+
+@pytest.mark.parametrize("S,N", [(3, 16), (600, 16), (2, 200)])
+def test_compact_result_form_is_the_same_answer(M, O, S, N):
+    # mpccbf_step_batch_host_compact returns the 6 whitened free dof per agent instead of the n control
+    # points; expanding them on the host reproduces mpccbf_step_batch_host bit for bit (both kernels: the
+    # lane-group kernel for small batches, the thread-per-agent kernel beyond).
+    cfg = M.default_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N, max_scenarios=S)
+    h = M.Handle(cfg)
+    st, tg = swarm(S, N, seed=S + N)
+    st[:, :, :2] *= 0.5 * N / 16
+    tg[:, :, :2] *= 0.5 * N / 16
+    st[0, 0, 3] = 2.5  # one infeasible agent: zeros in both forms
+    full = h.step_batch_host(st, tg)
+    comp = h.step_batch_host_compact(st, tg)
+    for k in ("status", "n_curves", "objective"):
+        assert np.array_equal(full[k], comp[k]), k
+    assert np.array_equal(h.expand_ctrl_pts(st, comp["v_free"], comp["n_curves"]).reshape(S, N, -1), full["ctrl_pts"])
+    assert (comp["v_free"][0, 0] == 0).all() and full["n_curves"][0, 0] == 0
+    # the driver's state advance straight from the compact record
+    oc = O.base_config(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N)
+    pos = h.eval_compact(st, comp["v_free"], cfg.h, 0).reshape(S, N, 3)
+    a = int(np.argmax(full["n_curves"][S - 1] > 0))
+    assert np.abs(pos[S - 1, a] - O.eval_curve(oc, full["ctrl_pts"][S - 1, a], cfg.h, 0)).max() <= 1e-12
+    h.close()
