@@ -242,7 +242,8 @@ int mpccbf_conn_rows(mpccbf_handle* h, int32_t num_scenarios, const double* stat
  *      mpc_cbf/examples/connectivity/MPCCBFFormationControl_example.cpp:135-231
  * (an agent whose optimize fails keeps following its previous curve, the parameter clamped to
  * max_parameter; one that never had a curve stays put with zero velocity), and the success metric of
- *      workspace/experiments/python/metrics/collision_check.py:48-79  (instance_success, circle shape)
+ *      workspace/experiments/python/metrics/collision_check.py:48-79  (instance_success; circle shape
+ *      here, the box shape through mpccbf_run_episode_ex)
  * is updated at every sub-step.
  *   states       [S][N][6]  in: start states, out: final states            device pointer
  *   targets      [S][N][3]  goals (tasks.sf)                               device pointer
@@ -265,6 +266,8 @@ int mpccbf_run_episode(mpccbf_handle* h, int32_t num_scenarios, double* states, 
 #define MPCCBF_ORDER_JACOBI 0        /* every agent optimises on the same snapshot (one launch per step)   */
 #define MPCCBF_ORDER_GAUSS_SEIDEL 1  /* the reference's loop order (MPCCBFFormationControl_example.cpp:140):
                                         agent i optimises and advances before agent i + 1 optimises        */
+#define MPCCBF_SHAPE_CIRCLE 0
+#define MPCCBF_SHAPE_BOX 1
 typedef struct mpccbf_episode_opts {
     double goal_radius;       /* reach_goal_area radius                                               */
     double collision_radius;  /* robot_params.collision_shape.radius                                   */
@@ -274,9 +277,19 @@ typedef struct mpccbf_episode_opts {
                                  component at every sub-step); 0 = noise-free                          */
     uint64_t seed;            /* the reference draws from random_device; here the noise is a
                                  counter-based stream of (seed, scenario, agent, sub-step)             */
+    int32_t collision_shape;  /* MPCCBF_SHAPE_CIRCLE (dist <= 2 r) or MPCCBF_SHAPE_BOX: the axis-aligned
+                                 rectangle test of collision_check.py:10-39 with its offsets (corner at
+                                 centre - half/2, width 2*half)                                        */
+    double box_half[2];       /* robot_params.collision_shape.aligned_box[0..1]                        */
 } mpccbf_episode_opts;
 
-/* Same as mpccbf_run_episode with the loop order and the state noise of the reference driver. */
+/* Fills goal_radius (1, the metric's default), collision_radius / collision_shape / box_half from
+ * robot_params.collision_shape of a reference experiment JSON with the metric's own precedence
+ * (collision_check.py:93-101: "aligned_box" first, else "radius"); order Jacobi, no noise. Host only. */
+int mpccbf_episode_opts_from_json(const char* path, mpccbf_episode_opts* opts);
+
+/* Same as mpccbf_run_episode with the loop order, the state noise and the collision shape of the
+ * reference driver / metric. */
 int mpccbf_run_episode_ex(mpccbf_handle* h, int32_t num_scenarios, double* states, const double* targets,
                           int32_t num_control_steps, const mpccbf_episode_opts* opts, int32_t* success,
                           int32_t* finish_step, double* min_dist, int32_t* failed_calls, double* traj,
@@ -305,6 +318,50 @@ int mpccbf_step_agents(mpccbf_handle* h, int32_t num_scenarios, int32_t agent_be
                        int32_t agent_count, const double* states, const double* targets,
                        double* ctrl_pts, int32_t* status, int32_t* n_curves, double* objective,
                        void* cuda_stream);
+
+/* Curve following of the reference driver for an agent shard, stateful per handle (curve being followed,
+ * its evaluation time, "has a curve" flag per agent): agents [agent_begin, agent_begin + agent_count) adopt
+ * their new curve where n_curves > 0 (evaluation time back to 0), then advance h / Ts sub-steps of Ts along
+ * the curve they follow, the parameter clamped to max_parameter; an agent that never had a curve keeps its
+ * position with zero velocity (MPCCBFFormationControl_example.cpp:161-221). Their rows of `states`
+ * ([S][N][6], the FULL snapshot) are updated in place; ctrl_new / n_curves are [S][agent_count][..].
+ * mpccbf_follow_reset forgets every curve. Device pointers, async on stream. */
+int mpccbf_follow_reset(mpccbf_handle* h, int32_t num_scenarios, void* cuda_stream);
+int mpccbf_follow_step(mpccbf_handle* h, int32_t num_scenarios, int32_t agent_begin, int32_t agent_count,
+                       double* states, const double* ctrl_new, const int32_t* n_curves, void* cuda_stream);
+
+/* Which fused kernel the controller entries run: -1 = by batch size (default), 0 = one thread per agent,
+ * 8 / 32 = that many lanes per agent. mpccbf_auto_kernel_variant returns what -1 resolves to for a step of
+ * `num_agent_qps` agents. (One agent's arithmetic does not depend on the batch it is solved in, only on the
+ * variant: pinning it makes sharded and unsharded runs agree bit for bit.) */
+int mpccbf_set_kernel_variant(mpccbf_handle* h, int32_t lanes);
+int32_t mpccbf_auto_kernel_variant(const mpccbf_handle* h, int64_t num_agent_qps);
+
+/* ---- Multi-GPU behind the ABI: one process, one host thread + stream per device ------------
+ * mpccbf_multi_create builds one handle per device (devices == NULL: ordinals 0..num_devices-1; cfg->device is
+ * ignored, cfg->max_scenarios is PER DEVICE) and, for more than one device, an NCCL communicator per device
+ * (ncclCommInitAll; libnccl.so.2 is loaded on demand). The reference's only fan-out is a shell loop over
+ * processes (experiments/bash/ScaleScript.sh:17-34). */
+typedef struct mpccbf_multi mpccbf_multi;
+int mpccbf_multi_create(const mpccbf_config* cfg, int32_t num_devices, const int32_t* devices, mpccbf_multi** out);
+int mpccbf_multi_destroy(mpccbf_multi* m);
+int32_t mpccbf_multi_num_devices(const mpccbf_multi* m);
+int32_t mpccbf_multi_comm_ranks(const mpccbf_multi* m);      /* ranks the NCCL communicator reports (1 without NCCL) */
+mpccbf_handle* mpccbf_multi_handle(mpccbf_multi* m, int32_t index);  /* the per-device handle (owned by m)   */
+/* Scenario sharding: same contract as mpccbf_step_batch_host / _host_compact (HOST pointers, pinned for
+ * overlap), scenarios split contiguously across the devices, no collective. */
+int mpccbf_multi_step_batch_host(mpccbf_multi* m, int32_t num_scenarios, const double* states, const double* targets,
+                                 double* ctrl_pts, int32_t* status, int32_t* n_curves, double* objective);
+int mpccbf_multi_step_batch_host_compact(mpccbf_multi* m, int32_t num_scenarios, const double* states,
+                                         const double* targets, double* v_free, int32_t* status, int32_t* n_curves,
+                                         double* objective);
+/* Agent sharding (BASELINE configs[3]): `num_control_steps` closed-loop control steps of num_scenarios swarms whose
+ * num_agents agents are split evenly across the devices: per step and device mpccbf_step_agents on the full
+ * snapshot -> mpccbf_follow_step -> ONE ncclAllGather of the [S][N/G][6] new states. states [S][N][6] HOST, in:
+ * start, out: final; targets [S][N][3] HOST. *ms_per_step (may be NULL): device time per control step, max over
+ * the devices. The result does not depend on the number of devices (bit for bit). */
+int mpccbf_multi_run_sharded(mpccbf_multi* m, int32_t num_scenarios, double* states, const double* targets,
+                             int32_t num_control_steps, double* ms_per_step);
 
 /* Active-set iteration counts of the last mpccbf_step_batch / _agents call on this handle:
  * iters [S][agents][impc_iter] (device pointer, valid until the next call), for flop accounting. */

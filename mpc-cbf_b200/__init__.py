@@ -35,7 +35,11 @@ EXPORTED_SYMBOLS = [
     "mpccbf_cbf_filter_batch", "mpccbf_cbf_filter_batch_host", "mpccbf_conn_rows", "mpccbf_run_episode",
     "mpccbf_run_episode_ex", "mpccbf_step_batch_host_async", "mpccbf_synchronize", "mpccbf_slack_fallback_count",
     "mpccbf_step_batch_compact", "mpccbf_step_batch_host_compact", "mpccbf_step_batch_host_compact_async",
-    "mpccbf_expand_ctrl_pts", "mpccbf_eval_compact",
+    "mpccbf_expand_ctrl_pts", "mpccbf_eval_compact", "mpccbf_episode_opts_from_json",
+    "mpccbf_follow_reset", "mpccbf_follow_step", "mpccbf_set_kernel_variant", "mpccbf_auto_kernel_variant",
+    "mpccbf_multi_create", "mpccbf_multi_destroy", "mpccbf_multi_num_devices", "mpccbf_multi_comm_ranks",
+    "mpccbf_multi_handle", "mpccbf_multi_step_batch_host", "mpccbf_multi_step_batch_host_compact",
+    "mpccbf_multi_run_sharded",
 ]
 
 
@@ -77,10 +81,21 @@ class Config(C.Structure):
 class EpisodeOpts(C.Structure):
     """Mirror of `mpccbf_episode_opts` (include/mpccbf.h)."""
     _fields_ = [("goal_radius", C.c_double), ("collision_radius", C.c_double), ("order", C.c_int32),
-                ("pos_std", C.c_double), ("vel_std", C.c_double), ("seed", C.c_uint64)]
+                ("pos_std", C.c_double), ("vel_std", C.c_double), ("seed", C.c_uint64),
+                ("collision_shape", C.c_int32), ("box_half", C.c_double * 2)]
 
 
 ORDER_JACOBI, ORDER_GAUSS_SEIDEL = 0, 1
+SHAPE_CIRCLE, SHAPE_BOX = 0, 1
+
+
+def episode_opts_from_json(path):
+    """collision shape of a reference experiment file with the metric's precedence (aligned_box first)."""
+    o = EpisodeOpts()
+    rc = lib().mpccbf_episode_opts_from_json(os.fsencode(path), C.byref(o))
+    if rc != OK:
+        raise MpcCbfError(rc, lib().mpccbf_last_error().decode())
+    return o
 
 
 class MpcCbfError(RuntimeError):
@@ -129,6 +144,20 @@ def lib(path=None):
     L.mpccbf_step_batch_host.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
     L.mpccbf_step_batch_host_async.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
     L.mpccbf_synchronize.argtypes = [vp]
+    L.mpccbf_episode_opts_from_json.argtypes = [C.c_char_p, vp]
+    L.mpccbf_follow_reset.argtypes = [vp, i32, vp]
+    L.mpccbf_follow_step.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp]
+    L.mpccbf_set_kernel_variant.argtypes = [vp, i32]
+    L.mpccbf_auto_kernel_variant.argtypes = [vp, i64]
+    L.mpccbf_multi_create.argtypes = [cfgp, i32, vp, C.POINTER(vp)]
+    L.mpccbf_multi_destroy.argtypes = [vp]
+    L.mpccbf_multi_num_devices.argtypes = [vp]
+    L.mpccbf_multi_comm_ranks.argtypes = [vp]
+    L.mpccbf_multi_handle.argtypes = [vp, i32]
+    L.mpccbf_multi_handle.restype = vp
+    L.mpccbf_multi_step_batch_host.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+    L.mpccbf_multi_step_batch_host_compact.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+    L.mpccbf_multi_run_sharded.argtypes = [vp, i32, vp, vp, i32, vp]
     L.mpccbf_step_batch_compact.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, vp]
     L.mpccbf_step_batch_host_compact.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
     L.mpccbf_step_batch_host_compact_async.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
@@ -371,14 +400,18 @@ class Handle:
 
     def run_episode(self, S, states, targets, steps, goal_radius, collision_radius, success=None, finish_step=None,
                     min_dist=None, failed_calls=None, traj=None, stream=None, order=ORDER_JACOBI, pos_std=0.0,
-                    vel_std=0.0, seed=0):
-        """Closed-loop episode on the device (states is updated in place); see include/mpccbf.h."""
-        if order == ORDER_JACOBI and pos_std == 0.0 and vel_std == 0.0:
+                    vel_std=0.0, seed=0, box_half=None):
+        """Closed-loop episode on the device (states is updated in place); see include/mpccbf.h.
+        box_half = (cx, cy): the metric's box collision shape instead of the circle."""
+        if order == ORDER_JACOBI and pos_std == 0.0 and vel_std == 0.0 and box_half is None:
             self._check(self._L.mpccbf_run_episode(self._h, S, _ptr(states), _ptr(targets), steps, goal_radius,
                                                    collision_radius, _ptr(success), _ptr(finish_step), _ptr(min_dist),
                                                    _ptr(failed_calls), _ptr(traj), stream))
             return
         o = EpisodeOpts(goal_radius, collision_radius, order, pos_std, vel_std, seed)
+        if box_half is not None:
+            o.collision_shape = SHAPE_BOX
+            o.box_half[:] = [float(box_half[0]), float(box_half[1])]
         self._check(self._L.mpccbf_run_episode_ex(self._h, S, _ptr(states), _ptr(targets), steps, C.byref(o),
                                                   _ptr(success), _ptr(finish_step), _ptr(min_dist),
                                                   _ptr(failed_calls), _ptr(traj), stream))
@@ -393,6 +426,20 @@ class Handle:
     def rollout_agents(self, S, agent_count, states, ctrl_pts, n_curves, next_states, stream=None):
         self._check(self._L.mpccbf_rollout_agents(self._h, S, agent_count, _ptr(states), _ptr(ctrl_pts),
                                                   _ptr(n_curves), _ptr(next_states), stream))
+
+    def follow_reset(self, S, stream=None):
+        self._check(self._L.mpccbf_follow_reset(self._h, S, stream))
+
+    def follow_step(self, S, agent_begin, agent_count, states, ctrl_new, n_curves, stream=None):
+        """Reference-driver curve following of an agent shard; `states` [S][N][6] is updated in place."""
+        self._check(self._L.mpccbf_follow_step(self._h, S, agent_begin, agent_count, _ptr(states), _ptr(ctrl_new),
+                                               _ptr(n_curves), stream))
+
+    def set_kernel_variant(self, lanes):
+        self._check(self._L.mpccbf_set_kernel_variant(self._h, lanes))
+
+    def auto_kernel_variant(self, num_agent_qps):
+        return int(self._L.mpccbf_auto_kernel_variant(self._h, num_agent_qps))
 
     def slack_fallback_count(self):
         """Always 0 since round 2 (the slack caps live in the active-set kernel; kept for round-1 callers)."""
@@ -417,3 +464,56 @@ class Handle:
         a, b = C.c_int64(), C.c_int64()
         self._L.mpccbf_get_counters(self._h, C.byref(a), C.byref(b))
         return a.value, b.value
+
+
+class Multi:
+    """RAII wrapper of `mpccbf_multi`: one process driving several GPUs through the C ABI."""
+
+    def __init__(self, cfg, num_devices, devices=None):
+        self._L = lib()
+        self.cfg = cfg
+        self._m = C.c_void_p()
+        dv = None
+        if devices is not None:
+            dv = (C.c_int32 * num_devices)(*devices)
+        rc = self._L.mpccbf_multi_create(C.byref(cfg), num_devices, dv, C.byref(self._m))
+        if rc != OK:
+            raise MpcCbfError(rc, self._L.mpccbf_last_error().decode())
+        self.num_devices = int(self._L.mpccbf_multi_num_devices(self._m))
+        self.comm_ranks = int(self._L.mpccbf_multi_comm_ranks(self._m))
+        self.n = cfg.n
+
+    def _check(self, rc):
+        if rc != OK:
+            raise MpcCbfError(rc, self._L.mpccbf_last_error().decode())
+
+    def step_batch_host(self, states, targets, out=None, compact=False):
+        states, targets = _f64(states), _f64(targets)
+        S, N = states.shape[0], states.shape[1]
+        it = self.cfg.impc_iter
+        key = "v_free" if compact else "ctrl_pts"
+        if out is None:
+            out = {key: np.zeros((S, N, 6 if compact else self.n)), "status": np.zeros((S, N, it), dtype=np.int32),
+                   "n_curves": np.zeros((S, N), dtype=np.int32), "objective": np.zeros((S, N))}
+        fn = self._L.mpccbf_multi_step_batch_host_compact if compact else self._L.mpccbf_multi_step_batch_host
+        self._check(fn(self._m, S, states.ctypes.data, targets.ctypes.data, _ptr(out[key]), _ptr(out["status"]),
+                       _ptr(out["n_curves"]), _ptr(out["objective"])))
+        return out
+
+    def run_sharded(self, states, targets, steps):
+        """Agent-sharded closed loop; returns (final states [S][N][6], device ms per control step)."""
+        st, tg = _f64(states).copy(), _f64(targets)
+        ms = C.c_double()
+        self._check(self._L.mpccbf_multi_run_sharded(self._m, st.shape[0], st.ctypes.data, tg.ctypes.data, steps, C.byref(ms)))
+        return st, ms.value
+
+    def close(self):
+        if self._m:
+            self._L.mpccbf_multi_destroy(self._m)
+            self._m = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

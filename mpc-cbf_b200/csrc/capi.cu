@@ -242,6 +242,69 @@ int build_device_tables(mpccbf_handle* h) {
     return MPCCBF_OK;
 }
 
+int ensure_episode_ws(mpccbf_handle* h) {
+    if (h->e_curve) return MPCCBF_OK;
+    const size_t B = static_cast<size_t>(h->cfg.max_scenarios) * h->cfg.num_agents, n = h->tab.n, it = h->cfg.impc_iter;
+    const int nsub = static_cast<int>(h->cfg.h / h->cfg.Ts);
+    bool ok = true;
+    ok &= cudaMalloc(&h->e_curve, sizeof(double) * B * n) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_ctrl, sizeof(double) * B * n) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_evalt, sizeof(double) * B) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_sub, sizeof(double) * B * std::max(nsub, 1) * 2) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_tg, sizeof(double) * h->cfg.max_scenarios * 3) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_has, sizeof(int32_t) * B) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_nc, sizeof(int32_t) * B) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_status, sizeof(int32_t) * B * it) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_reached, B) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_mind2, sizeof(double) * h->cfg.max_scenarios) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_done, sizeof(int32_t) * h->cfg.max_scenarios) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_finish, sizeof(int32_t) * h->cfg.max_scenarios) == cudaSuccess;
+    ok &= cudaMalloc(&h->e_failed, sizeof(int32_t) * h->cfg.max_scenarios) == cudaSuccess;
+    if (!ok) {
+        set_error("episode / curve-following workspace: out of device memory");
+        return MPCCBF_ERR_ALLOC;
+    }
+    return MPCCBF_OK;
+}
+
+// the handle-constant part of EpisodeArgs
+void fill_episode_consts(const mpccbf_handle* h, EpisodeArgs& a) {
+    a.curve = h->e_curve; a.eval_t = h->e_evalt; a.has_curve = h->e_has; a.reached = h->e_reached;
+    a.done = h->e_done; a.finish = h->e_finish; a.min_dist2 = h->e_mind2; a.failed = h->e_failed;
+    a.sub = h->e_sub;
+    a.N = h->cfg.num_agents; a.n = h->tab.n; a.c = h->tab.c; a.p = h->tab.p; a.iters = h->cfg.impc_iter;
+    a.nsub = static_cast<int>(h->cfg.h / h->cfg.Ts);
+    a.Ts = h->cfg.Ts; a.piece_T = h->cfg.piece_max_param;
+    double cum = 0.0;
+    for (int i = 0; i < 16; ++i) {
+        if (i < h->tab.p) cum += h->cfg.piece_max_param;  // cumulative ends by repeated addition, like the reference
+        a.cum[i] = cum;
+    }
+    a.max_param = cum;
+    a.final_only = 0;
+    a.box = 0; a.box_x = a.box_y = 0.0;
+    a.goal_radius = a.collision_radius = 0.0;
+    a.pos_std = a.vel_std = 0.0; a.seed = 0;
+    a.traj = nullptr; a.traj_len = 0; a.step = 0;
+}
+
+// Which fused kernel a step of `num_qp` agent-QPs runs: 0 = thread-per-agent, 8 / 32 = lanes per agent.
+int resolve_lanes(const mpccbf_handle* h, int64_t num_qp, bool force_auto = false) {
+    int lanes = force_auto ? -1 : h->lanes;
+    if (lanes < 0) {
+        // Measured crossover on B200 (profiles/r1h_kernel_crossover.md): a warp per agent (32 lanes split
+        // the row scan) wins while all its warps fit in one wave of 8 per SM — twice that for dense swarms,
+        // where a scan walks hundreds of safety rows; the thread-per-agent kernel wins beyond. The 8-lane
+        // variant is only the large-batch fallback for configurations without the polynomial row structure.
+        const int wave = 8 * h->sm_count * (h->cfg.num_agents >= 128 ? 2 : 1);
+        lanes = (num_qp <= wave) ? 32 : 0;
+    }
+    if (h->cfg.slack_mode) lanes = 0;  // capped multipliers live in the thread-per-agent kernel only
+    if (lanes == 0 && !h->dev.poly)  // the thread kernel needs the polynomial row structure
+        lanes = (num_qp >= 2048 && h->cfg.num_agents < 64) ? 8 : 32;
+    return lanes;
+}
+
 int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_count, const double* states,
              const double* targets, int ref_mode, double* ctrl, double* ctrl_all, double* v_out, int32_t* status,
              int32_t* n_curves, double* objective, int32_t* iters, cudaStream_t stream) {
@@ -265,18 +328,7 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
     a.lead_ws = h->w_lead;
-    int lanes = h->lanes;
-    if (lanes < 0) {
-        // Measured crossover on B200 (profiles/r1h_kernel_crossover.md): a warp per agent (32 lanes split
-        // the row scan) wins while all its warps fit in one wave of 8 per SM — twice that for dense swarms,
-        // where a scan walks hundreds of safety rows; the thread-per-agent kernel wins beyond. The 8-lane
-        // variant is only the large-batch fallback for configurations without the polynomial row structure.
-        const int wave = 8 * h->sm_count * (h->cfg.num_agents >= 128 ? 2 : 1);
-        lanes = (a.num_qp <= wave) ? 32 : 0;
-    }
-    if (h->cfg.slack_mode) lanes = 0;  // capped multipliers live in the thread-per-agent kernel only
-    if (lanes == 0 && !h->dev.poly)  // the thread kernel needs the polynomial row structure
-        lanes = (a.num_qp >= 2048 && h->cfg.num_agents < 64) ? 8 : 32;
+    const int lanes = resolve_lanes(h, a.num_qp);
     if (lanes == 0)
         CUDA_TRY(launch_impc_thread(h->dev, a, h->sm_count, stream));
     else
@@ -424,6 +476,19 @@ int mpccbf_destroy(mpccbf_handle* h) {
 }
 
 int32_t mpccbf_num_decision_vars(const mpccbf_handle* h) { return h ? h->tab.n : 0; }
+
+int mpccbf_set_kernel_variant(mpccbf_handle* h, int32_t lanes) {
+    if (!h || !(lanes == -1 || lanes == 0 || lanes == 8 || lanes == 32)) {
+        set_error("mpccbf_set_kernel_variant: lanes must be -1 (auto), 0 (thread per agent), 8 or 32");
+        return MPCCBF_ERR_INVALID;
+    }
+    h->lanes = lanes;
+    return MPCCBF_OK;
+}
+int32_t mpccbf_auto_kernel_variant(const mpccbf_handle* h, int64_t num_agent_qps) {
+    if (!h) return -1;
+    return resolve_lanes(h, num_agent_qps, true);
+}
 int32_t mpccbf_active_solver(const mpccbf_handle* h) { return h ? h->solver : 0; }
 
 void* mpccbf_host_alloc(size_t bytes) {
@@ -813,7 +878,8 @@ int mpccbf_run_episode_ex(mpccbf_handle* h, int32_t S, double* states, const dou
     int rc = require_device(h);
     if (rc != MPCCBF_OK) return rc;
     if (S < 0 || S > h->cfg.max_scenarios || steps < 0 || !states || !targets || !opts ||
-        (opts->order != MPCCBF_ORDER_JACOBI && opts->order != MPCCBF_ORDER_GAUSS_SEIDEL) || opts->pos_std < 0 || opts->vel_std < 0) {
+        (opts->order != MPCCBF_ORDER_JACOBI && opts->order != MPCCBF_ORDER_GAUSS_SEIDEL) || opts->pos_std < 0 || opts->vel_std < 0 ||
+        (opts->collision_shape != MPCCBF_SHAPE_CIRCLE && opts->collision_shape != MPCCBF_SHAPE_BOX)) {
         set_error("mpccbf_run_episode: invalid argument (num_scenarios must be <= max_scenarios)");
         return MPCCBF_ERR_INVALID;
     }
@@ -824,47 +890,21 @@ int mpccbf_run_episode_ex(mpccbf_handle* h, int32_t S, double* states, const dou
     if (S == 0) return MPCCBF_OK;
     CUDA_TRY(cudaSetDevice(h->device));
     cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
-    const size_t B = static_cast<size_t>(h->cfg.max_scenarios) * h->cfg.num_agents, n = h->tab.n, it = h->cfg.impc_iter;
     const int nsub = static_cast<int>(h->cfg.h / h->cfg.Ts);  // int(h / Ts), MPCCBFFormationControl_example.cpp:193
-    if (!h->e_curve) {
-        bool ok = true;
-        ok &= cudaMalloc(&h->e_curve, sizeof(double) * B * n) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_ctrl, sizeof(double) * B * n) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_evalt, sizeof(double) * B) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_sub, sizeof(double) * B * std::max(nsub, 1) * 2) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_tg, sizeof(double) * h->cfg.max_scenarios * 3) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_has, sizeof(int32_t) * B) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_nc, sizeof(int32_t) * B) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_status, sizeof(int32_t) * B * it) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_reached, B) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_mind2, sizeof(double) * h->cfg.max_scenarios) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_done, sizeof(int32_t) * h->cfg.max_scenarios) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_finish, sizeof(int32_t) * h->cfg.max_scenarios) == cudaSuccess;
-        ok &= cudaMalloc(&h->e_failed, sizeof(int32_t) * h->cfg.max_scenarios) == cudaSuccess;
-        if (!ok) {
-            set_error("mpccbf_run_episode: out of device memory");
-            return MPCCBF_ERR_ALLOC;
-        }
-    }
+    rc = ensure_episode_ws(h);
+    if (rc != MPCCBF_OK) return rc;
     const int N = h->cfg.num_agents;
     CUDA_TRY(launch_episode_init(S, N, h->e_evalt, h->e_has, h->e_reached, h->e_done, h->e_finish, h->e_mind2, h->e_failed, st));
     EpisodeArgs a;
+    fill_episode_consts(h, a);
     a.states = states; a.targets = targets; a.ctrl_new = h->e_ctrl; a.n_curves = h->e_nc;
-    a.curve = h->e_curve; a.eval_t = h->e_evalt; a.has_curve = h->e_has; a.reached = h->e_reached;
-    a.done = h->e_done; a.finish = h->e_finish; a.min_dist2 = h->e_mind2; a.failed = h->e_failed; a.traj = traj;
-    a.sub = h->e_sub;
-    a.S = S; a.N = N; a.n = h->tab.n; a.c = h->tab.c; a.p = h->tab.p; a.iters = h->cfg.impc_iter;
-    a.nsub = nsub;
+    a.traj = traj;
+    a.S = S;
     a.traj_len = steps * a.nsub;
-    a.Ts = h->cfg.Ts; a.piece_T = h->cfg.piece_max_param;
     a.goal_radius = opts->goal_radius; a.collision_radius = opts->collision_radius;
+    a.box = opts->collision_shape == MPCCBF_SHAPE_BOX ? 1 : 0;
+    a.box_x = opts->box_half[0]; a.box_y = opts->box_half[1];
     a.pos_std = opts->pos_std; a.vel_std = opts->vel_std; a.seed = opts->seed;
-    double cum = 0.0;
-    for (int i = 0; i < 16; ++i) {
-        if (i < h->tab.p) cum += h->cfg.piece_max_param;  // cumulative ends by repeated addition, like the reference
-        a.cum[i] = cum;
-    }
-    a.max_param = cum;
     for (int step = 0; step < steps; ++step) {
         a.step = step;
         if (opts->order == MPCCBF_ORDER_JACOBI) {
@@ -898,7 +938,52 @@ int mpccbf_run_episode(mpccbf_handle* h, int32_t S, double* states, const double
     o.order = MPCCBF_ORDER_JACOBI;
     o.pos_std = o.vel_std = 0.0;
     o.seed = 0;
+    o.collision_shape = MPCCBF_SHAPE_CIRCLE;
+    o.box_half[0] = o.box_half[1] = 0.0;
     return mpccbf_run_episode_ex(h, S, states, targets, steps, &o, success, finish_step, min_dist, failed_calls, traj, cuda_stream);
+}
+
+int mpccbf_follow_reset(mpccbf_handle* h, int32_t S, void* cuda_stream) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (S < 0 || S > h->cfg.max_scenarios) {
+        set_error("mpccbf_follow_reset: invalid argument (num_scenarios must be <= max_scenarios)");
+        return MPCCBF_ERR_INVALID;
+    }
+    CUDA_TRY(cudaSetDevice(h->device));
+    rc = ensure_episode_ws(h);
+    if (rc != MPCCBF_OK) return rc;
+    CUDA_TRY(launch_episode_init(S, h->cfg.num_agents, h->e_evalt, h->e_has, h->e_reached, h->e_done, h->e_finish, h->e_mind2,
+                                 h->e_failed, static_cast<cudaStream_t>(cuda_stream)));
+    return MPCCBF_OK;
+}
+
+int mpccbf_follow_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_count, double* states,
+                       const double* ctrl_new, const int32_t* n_curves, void* cuda_stream) {
+    int rc = require_device(h);
+    if (rc != MPCCBF_OK) return rc;
+    if (S < 0 || S > h->cfg.max_scenarios || agent_begin < 0 || agent_count < 0 || agent_begin + agent_count > h->cfg.num_agents ||
+        !states || !ctrl_new || !n_curves) {
+        set_error("mpccbf_follow_step: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (h->tab.c > 8 || h->tab.p > 16) {
+        set_error("mpccbf_follow_step: curves with more than 8 control points or 16 pieces are not supported");
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    if (S == 0 || agent_count == 0) return MPCCBF_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    rc = ensure_episode_ws(h);
+    if (rc != MPCCBF_OK) return rc;
+    EpisodeArgs a;
+    fill_episode_consts(h, a);
+    a.states = states; a.targets = nullptr; a.ctrl_new = ctrl_new; a.n_curves = n_curves;
+    a.S = S;
+    a.agent_begin = agent_begin; a.agent_count = agent_count; a.do_metrics = 0;
+    a.final_only = 1;
+    CUDA_TRY(launch_episode_advance(a, h->sm_count, static_cast<cudaStream_t>(cuda_stream)));
+    h->launches += 1;
+    return MPCCBF_OK;
 }
 
 int mpccbf_rollout(mpccbf_handle* h, int32_t S, const double* states, const double* ctrl_pts,

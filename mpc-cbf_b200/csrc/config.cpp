@@ -190,4 +190,44 @@ int mpccbf_config_from_json(const char* path, mpccbf_config* c, double* so, doub
     return mpccbf_config_validate(c);
 }
 
+
+int mpccbf_episode_opts_from_json(const char* path, mpccbf_episode_opts* o) {
+    if (!path || !o) {
+        set_error("mpccbf_episode_opts_from_json: NULL argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    try {
+        std::ifstream f(path);
+        if (!f) {
+            set_error(std::string("cannot open ") + path);
+            return MPCCBF_ERR_INVALID;
+        }
+        std::stringstream ss;
+        ss << f.rdbuf();
+        const std::string text = ss.str();
+        mpccbf::JsonParser parser(text);
+        const mpccbf::JsonValue j = parser.parse();
+        std::memset(o, 0, sizeof(*o));
+        o->goal_radius = 1.0;  // instance_success(..., radius=1, ...) collision_check.py:104
+        o->order = MPCCBF_ORDER_JACOBI;
+        const auto& shape = j.at("robot_params").at("collision_shape");
+        if (shape.has("aligned_box")) {  // collision_check.py:93-101: aligned_box wins over radius
+            o->collision_shape = MPCCBF_SHAPE_BOX;
+            o->box_half[0] = shape.at("aligned_box").at(0).number();
+            o->box_half[1] = shape.at("aligned_box").at(1).number();
+            if (shape.has("radius")) o->collision_radius = shape.at("radius").number();
+        } else if (shape.has("radius")) {
+            o->collision_shape = MPCCBF_SHAPE_CIRCLE;
+            o->collision_radius = shape.at("radius").number();
+        } else {
+            set_error("Missing collision shape: must provide either 'aligned_box' or 'radius'");
+            return MPCCBF_ERR_INVALID;
+        }
+    } catch (const std::exception& e) {
+        set_error(std::string("mpccbf_episode_opts_from_json: ") + e.what());
+        return MPCCBF_ERR_INVALID;
+    }
+    return MPCCBF_OK;
+}
+
 }  // extern "C"

@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(128) episode_advance_kernel(const EpisodeArgs 
             const bool has = a.has_curve[g] != 0;
             const double t0 = a.eval_t[g];
             double hold[3] = {a.states[g * 6], a.states[g * 6 + 1], a.states[g * 6 + 2]};
-            for (int ti = 1; ti <= a.nsub; ++ti) {
+            for (int ti = a.final_only ? a.nsub : 1; ti <= a.nsub; ++ti) {
                 const int tglob = a.step * a.nsub + (ti - 1);
                 double st6[6];
                 if (has) {
@@ -185,7 +185,15 @@ __global__ void __launch_bounds__(128) episode_advance_kernel(const EpisodeArgs 
                     const double dx = pi[0] - pj[0], dy = pi[1] - pj[1];
                     const double d2 = dx * dx + dy * dy;
                     mind2 = fmin(mind2, d2);
-                    hit |= (d2 <= coll2) ? 1 : 0;
+                    if (a.box) {
+                        // collision_check.py:10-39: corner = centre - half / 2, width = 2 * half, strict inequalities
+                        const double xA = pi[0] - a.box_x / 2, yA = pi[1] - a.box_y / 2;
+                        const double xB = pj[0] - a.box_x / 2, yB = pj[1] - a.box_y / 2;
+                        const double w = 2 * a.box_x, hh = 2 * a.box_y;
+                        hit |= (xA < xB + w && xA + w > xB && yA < yB + hh && yA + hh > yB) ? 1 : 0;
+                    } else {
+                        hit |= (d2 <= coll2) ? 1 : 0;
+                    }
                 }
             }
             hit = __any_sync(full, hit);

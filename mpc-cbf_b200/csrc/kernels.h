@@ -63,7 +63,10 @@ struct EpisodeArgs {
     int S, N, n, c, p, iters, nsub, step, traj_len;
     int agent_begin, agent_count;  // phase A range; ctrl_new / n_curves are [S][agent_count][..]
     int do_metrics;            // phase B
+    int final_only;            // phase A evaluates only the last sub-step (no metrics, trajectory dump or noise wanted)
     double Ts, piece_T, max_param, goal_radius, collision_radius;
+    int box;                   // collision_check.py box shape instead of the circle
+    double box_x, box_y;
     double pos_std, vel_std;   // Gaussian state noise per sub-step (0: none)
     unsigned long long seed;
     double cum[16];            // cumulative piece ends

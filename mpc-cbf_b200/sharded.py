@@ -5,9 +5,11 @@ Two ways the path shards:
 * scenario sharding — independent scenarios are split contiguously across ranks, constant tables
   are replicated, and there is NO data-path collective (`scenario_range`);
 * agent sharding — ONE scenario's agents are split across ranks (BASELINE configs[3], 256 agents):
-  each rank solves its own agents against the full state snapshot with `mpccbf_step_agents`, rolls
-  them forward with `mpccbf_rollout_agents`, and a single all-gather of the `[S][N/G][6]` next
-  states per control step rebuilds the snapshot everywhere (`AgentShardedStepper`). The IMPC
+  each rank solves its own agents against the full state snapshot with `mpccbf_step_agents`, advances
+  them along their curves like the reference driver with `mpccbf_follow_step` (an agent whose optimize
+  failed keeps following its previous curve, MPCCBFFormationControl_example.cpp:161-221), and a single
+  all-gather of the `[S][N/G][6]` next states per control step rebuilds the snapshot everywhere
+  (`AgentShardedStepper`). The same loop without Python: `mpccbf_multi_run_sharded` (csrc/multi.cu). The IMPC
   iter-1 rows use the CURRENT neighbour states (ConnectivityIMPCCBF.cpp:174), so one exchange per
   control step suffices.
 
@@ -61,6 +63,8 @@ class AgentShardedStepper:
         self.S, self.N = num_scenarios, cfg.num_agents
         self.begin, self.cnt = agent_range(self.N, rank, world)
         self.h = module.Handle(cfg)
+        # every shard runs the kernel variant the unsharded step would run: the result does not depend on `world`
+        self.h.set_kernel_variant(self.h.auto_kernel_variant(self.S * self.N))
         n, it = self.h.n, cfg.impc_iter
         f64, i32 = torch.float64, torch.int32
         S, cnt = self.S, self.cnt
@@ -68,19 +72,23 @@ class AgentShardedStepper:
         self.status = torch.zeros((S, cnt, it), dtype=i32, device=device)
         self.n_curves = torch.zeros((S, cnt), dtype=i32, device=device)
         self.objective = torch.zeros((S, cnt), dtype=f64, device=device)
-        self.local_states = torch.zeros((S, cnt, 6), dtype=f64, device=device)
         self.local_next = torch.zeros((S, cnt, 6), dtype=f64, device=device)
         self.scratch = torch.empty((world, S, cnt, 6), dtype=f64, device=device) if (world > 1 and S > 1) else None
+        self.h.follow_reset(S, stream=torch.cuda.current_stream(device).cuda_stream if device.type == "cuda" else None)
 
     def step(self, states_full, targets_local, stream=None):
         """states_full [S][N][6] (same on every rank) is advanced IN PLACE by one control step.
-        targets_local [S][N/G][3]. Returns this rank's (ctrl_pts, status, n_curves)."""
-        sp = stream.cuda_stream if stream is not None else None
-        self.local_states.copy_(states_full[:, self.begin:self.begin + self.cnt, :])
-        self.h.step_agents(self.S, self.begin, self.cnt, states_full, targets_local, self.ctrl, self.status,
-                           self.n_curves, self.objective, stream=sp)
-        self.h.rollout_agents(self.S, self.cnt, self.local_states, self.ctrl, self.n_curves, self.local_next, stream=sp)
-        gather_states(self.local_next, states_full, self.world, self.group, self.scratch)
+        targets_local [S][N/G][3]. `stream`: a torch.cuda.Stream (default: the current one); the C-ABI calls, the
+        copies and the collective are all ordered on it. Returns this rank's (ctrl_pts, status, n_curves)."""
+        stream = stream if stream is not None else torch.cuda.current_stream(states_full.device)
+        sp = stream.cuda_stream
+        with torch.cuda.stream(stream):
+            self.h.step_agents(self.S, self.begin, self.cnt, states_full, targets_local, self.ctrl, self.status,
+                               self.n_curves, self.objective, stream=sp)
+            self.h.follow_step(self.S, self.begin, self.cnt, states_full, self.ctrl, self.n_curves, stream=sp)
+            if self.world > 1:
+                self.local_next.copy_(states_full[:, self.begin:self.begin + self.cnt, :])
+                gather_states(self.local_next, states_full, self.world, self.group, self.scratch)
         return self.ctrl, self.status, self.n_curves
 
     def close(self):

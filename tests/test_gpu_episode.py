@@ -201,3 +201,44 @@ def test_episode_noise_statistics(M):
     assert abs(c) < 0.05
     for h in (h0, h1, h2, h3):
         h.close()
+
+
+def instance_success_box(traj, goals, radius, half):
+    """collision_check.py:10-79 with shape_type == "box" (corner = centre - half / 2, width 2 * half)."""
+    N, T = traj.shape[:2]
+    cx, cy = half
+    reach = [False] * N
+    for t in range(T):
+        if all(reach):
+            return True, max(0, t - 1)
+        for i in range(N):
+            if np.linalg.norm(traj[i, t, :2] - goals[i][:2]) <= radius:
+                reach[i] = True
+            for j in range(i + 1, N):
+                xA, yA = traj[i, t, 0] - cx / 2, traj[i, t, 1] - cy / 2
+                xB, yB = traj[j, t, 0] - cx / 2, traj[j, t, 1] - cy / 2
+                if xA < xB + 2 * cx and xA + 2 * cx > xB and yA < yB + 2 * cy and yA + 2 * cy > yB:
+                    return False, -1
+    return True, T
+
+
+def test_episode_box_collision_shape_of_the_reference_configs(M):
+    # base_config.json / circle{2,8}.json carry "aligned_box": [0.2, 0.2, 0] next to "radius": the metric then
+    # uses the rectangle test (collision_check.py:93-101). Shape parsed from the golden config; box sizes from
+    # the file's own to one that makes some scenarios collide.
+    o = M.episode_opts_from_json(os.path.join(GOLDEN, "circle8_config.json"))
+    assert o.collision_shape == M.SHAPE_BOX and list(o.box_half) == [0.2, 0.2] and o.goal_radius == 1.0
+    S, N, steps = 12, 6, 40
+    cfg = M.default_config(k_hor=16, num_pieces=3, d_min=0.8, num_agents=N, max_scenarios=S)
+    st, tg = swarm(S, N, seed=9)
+    st[:, :, :2] *= 0.45
+    tg[:, :, :2] *= 0.45
+    seen = set()
+    for half in ((0.2, 0.2), (0.45, 0.3), (0.7, 0.7)):
+        h, res = run(M, cfg, st, tg, steps, 1.0, 0.2, box_half=half)
+        for s in range(S):
+            ok, fin = instance_success_box(res["traj"][s], tg[s], 1.0, half)
+            assert bool(res["success"][s]) == ok and int(res["finish"][s]) == fin, (half, s)
+            seen.add(ok)
+        h.close()
+    assert seen == {True, False}
