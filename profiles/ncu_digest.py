@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """Digest of an .ncu-rep (read in the build container): headline raw metrics of each captured launch
 and the share of executed warp instructions / stall samples per source line.
-usage: python profiles/ncu_digest.py gpurun_out/x.ncu-rep [top_lines]"""
+usage: python profiles/ncu_digest.py gpurun_out/x.ncu-rep [top_lines] [--json profiles/rNx_fused_kernel.json --agents A]
+With --json the per-launch DRAM traffic and executed FP64 flops of the LAST captured launch are written for bench.py
+(roofline.traffic / roofline.executed), stamped with the current commit."""
 import collections
 import csv
 import io
@@ -24,18 +26,63 @@ WANT = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "la
         "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio",
-        "smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio"]
+        "smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio",
+        "smsp__sass_thread_inst_executed_op_dfma_pred_on.sum", "smsp__sass_thread_inst_executed_op_dmul_pred_on.sum",
+        "smsp__sass_thread_inst_executed_op_dadd_pred_on.sum", "smsp__sass_thread_inst_executed_ops_dadd_dmul_dfma_pred_on.sum"]
 
 
 def ncu(rep, *args):
     return subprocess.run(["ncu", "-i", rep, *args], capture_output=True, text=True).stdout
 
 
+def to_bytes(val, unit):
+    mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    return float(val.replace(",", "")) * mult.get(unit, 1)
+
+
+def write_json(path, hdr, units, row, agents):
+    import datetime
+    import json
+    def get(name):
+        return (row[hdr.index(name)], units[hdr.index(name)]) if name in hdr else (None, None)
+    rd, wr = get("dram__bytes_read.sum"), get("dram__bytes_write.sum")
+    out = {"when": datetime.datetime.utcnow().isoformat() + "Z",
+           "commit": subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip(),
+           "kernel": row[hdr.index("Kernel Name")].split("(")[0], "agents_per_launch": agents}
+    if rd[0] is not None:
+        out["dram_bytes_per_launch"] = to_bytes(*rd) + to_bytes(*wr)
+    fl = 0.0
+    for name, w in (("dfma", 2.0), ("dmul", 1.0), ("dadd", 1.0)):
+        v, _ = get(f"smsp__sass_thread_inst_executed_op_{name}_pred_on.sum")
+        if v is not None:
+            out[f"thread_inst_{name}"] = float(v.replace(",", ""))
+            fl += w * out[f"thread_inst_{name}"]
+    if fl:
+        out["fp64_flops_executed_per_launch"] = fl
+    d, du = get("gpu__time_duration.sum")
+    if d is not None:
+        out["duration_us_under_ncu"] = float(d.replace(",", "")) * {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(du, 1.0)
+    json.dump(out, open(path, "w"), indent=1)
+    print("wrote", path, out)
+
+
 def main():
     rep = sys.argv[1]
-    top = int(sys.argv[2]) if len(sys.argv) > 2 else 30
+    argv = sys.argv[2:]
+    jpath, agents = None, None
+    if "--json" in argv:
+        i = argv.index("--json")
+        jpath = argv[i + 1]
+        del argv[i:i + 2]
+    if "--agents" in argv:
+        i = argv.index("--agents")
+        agents = int(argv[i + 1])
+        del argv[i:i + 2]
+    top = int(argv[0]) if argv else 30
     rows = list(csv.reader(io.StringIO(ncu(rep, "--page", "raw", "--csv"))))
     hdr, units, data = rows[0], rows[1], rows[2:]
+    if jpath:
+        write_json(jpath, hdr, units, data[-1], agents)
     print("kernel:", [r[hdr.index("Kernel Name")].split("(")[0] for r in data])
     for w in WANT:
         if w in hdr:
