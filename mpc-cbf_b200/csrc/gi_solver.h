@@ -1,12 +1,11 @@
 // Dual active-set (Goldfarb-Idnani, least-distance form) on a D-dimensional projection problem
 //      min 1/2 |v - v0|^2   s.t.   n_i . v >= rhs_i
-// with the whole factorisation (orthogonal J, triangular R of the active normals) in registers.
+// with the iterate, the multipliers and the ids of the active rows in registers.
 // Used by the thread-per-agent fused kernel with D = 4 (x/y axes, coupled by the CBF rows) and
 // D = 2 (yaw axis, decoupled). The state is resumable: gi_run can be called again after more rows
 // became visible to the row provider (the iterate of a sub-problem is a valid dual-feasible
-// starting point for the larger problem), and it can be rebuilt from the ids and multipliers of
-// its active rows alone (gi_rebuild), which is how the stage-A solution of an agent is restored
-// before a later IMPC iteration without keeping a copy of J and R.
+// starting point for the larger problem), and it is nothing but (v, u, ids) — which is how the stage-A
+// solution of an agent is restored before a later IMPC iteration.
 //
 // SOFT rows (slack mode, ConnectivityIMPCCBF.cpp:76-100 + MPCCBFQPGeneratorBase.cpp:28-38,80-135):
 // the safety rows of neighbour j share one slack variable s_j >= 0 with linear cost w_j. With the
@@ -38,36 +37,21 @@ namespace mpccbf {
 
 template <int D>
 struct GIState {
-    double J[D][D];
-    double Rm[D][D];  // upper triangular, leading q x q block used
     double u[D];      // multipliers of the active rows
     double v[D];      // current iterate
-    int id[D];        // row id of each active column
+    int id[D];        // row ids of the active set
     int q;            // number of active rows
 };
 
-// group bookkeeping of the active columns (SOFT rows only)
+// group bookkeeping of the active rows (SOFT rows only)
 template <int D>
 struct GISoft {
-    int grp[D];      // group of each active column (-1: hard row)
+    int grp[D];      // group of each active row (-1: hard row)
     double cap[D];   // weight of that group
 };
 
 template <int D>
-MPCCBF_HD void gi_reset_factor(GIState<D>& g) {
-#pragma unroll
-    for (int i = 0; i < D; ++i) {
-#pragma unroll
-        for (int j = 0; j < D; ++j) {
-            g.J[i][j] = (i == j) ? 1.0 : 0.0;
-            g.Rm[i][j] = 0.0;
-        }
-    }
-}
-
-template <int D>
 MPCCBF_HD void gi_init(GIState<D>& g, const double* v0) {
-    gi_reset_factor<D>(g);
 #pragma unroll
     for (int i = 0; i < D; ++i) {
         g.u[i] = 0.0;
@@ -77,104 +61,23 @@ MPCCBF_HD void gi_init(GIState<D>& g, const double* v0) {
     g.q = 0;
 }
 
-// d = J' n
-template <int D>
-MPCCBF_HD void gi_project(const GIState<D>& g, const double (&np)[D], double (&d)[D]) {
+// removes active row lpos from the lists
+template <int D, bool SOFT>
+MPCCBF_HD void gi_remove(GIState<D>& g, GISoft<D>& gs, int lpos) {
 #pragma unroll
-    for (int j = 0; j < D; ++j) {
-        double s = 0.0;
-#pragma unroll
-        for (int i = 0; i < D; ++i) s = fma(g.J[i][j], np[i], s);
-        d[j] = s;
-    }
-}
-
-// Appends the column whose projection is d = J' n: rotates d[q..] onto e_q (Givens from the bottom,
-// carried into J2) and stores R's new column. The caller sets u / id of the new column.
-template <int D>
-MPCCBF_HD void gi_add_column(GIState<D>& g, double (&d)[D]) {
-#pragma unroll
-    for (int k = D - 1; k >= 1; --k) {
-        if (k > g.q) {
-            const double a = d[k - 1], b = d[k];
-            const double hh = sqrt(fma(a, a, b * b));
-            if (hh > 0.0) {
-                const double ih = 1.0 / hh;
-                const double cs = a * ih, sn = b * ih;
-                d[k - 1] = hh;
-                d[k] = 0.0;
-#pragma unroll
-                for (int i = 0; i < D; ++i) {
-                    const double a1 = g.J[i][k - 1], a2 = g.J[i][k];
-                    g.J[i][k - 1] = fma(cs, a1, sn * a2);
-                    g.J[i][k] = fma(-sn, a1, cs * a2);
-                }
+    for (int c = 0; c < D - 1; ++c)
+        if (c >= lpos) {
+            g.u[c] = g.u[c + 1];
+            g.id[c] = g.id[c + 1];
+            if constexpr (SOFT) {
+                gs.grp[c] = gs.grp[c + 1];
+                gs.cap[c] = gs.cap[c + 1];
             }
-        }
-    }
-#pragma unroll
-    for (int col = 0; col < D; ++col)
-        if (col == g.q) {
-#pragma unroll
-            for (int i = 0; i <= col; ++i) g.Rm[i][col] = d[i];
-        }
-    ++g.q;
-}
-
-// Removes active column lpos (R becomes upper Hessenberg from there; Givens restore the triangle).
-template <int D>
-MPCCBF_HD void gi_drop_column(GIState<D>& g, int lpos) {
-#pragma unroll
-    for (int col = 0; col < D - 1; ++col)
-        if (col >= lpos) {
-#pragma unroll
-            for (int i = 0; i <= col + 1; ++i) g.Rm[i][col] = g.Rm[i][col + 1];  // Hessenberg part
-            g.u[col] = g.u[col + 1];
-            g.id[col] = g.id[col + 1];
         }
     g.u[D - 1] = 0.0;
     g.id[D - 1] = -1;
+    if constexpr (SOFT) gs.grp[D - 1] = -1;
     --g.q;
-#pragma unroll
-    for (int k = 0; k < D - 1; ++k)
-        if (k >= lpos && k < g.q) {
-            const double a = g.Rm[k][k], b = g.Rm[k + 1][k];
-            const double hh = sqrt(fma(a, a, b * b));
-            if (hh > 0.0) {
-                const double ih = 1.0 / hh;
-                const double cs = a * ih, sn = b * ih;
-#pragma unroll
-                for (int col = 0; col < D; ++col)
-                    if (col >= k) {
-                        // (the sub-diagonal entry b is annihilated; it is never read again)
-                        const double a1 = g.Rm[k][col], a2 = (col > k) ? g.Rm[k + 1][col] : b;
-                        g.Rm[k][col] = fma(cs, a1, sn * a2);
-                        if (col > k) g.Rm[k + 1][col] = fma(-sn, a1, cs * a2);
-                    }
-#pragma unroll
-                for (int i = 0; i < D; ++i) {
-                    const double a1 = g.J[i][k], a2 = g.J[i][k + 1];
-                    g.J[i][k] = fma(cs, a1, sn * a2);
-                    g.J[i][k + 1] = fma(-sn, a1, cs * a2);
-                }
-            }
-        }
-}
-
-// J, R from the ids of the active columns (u, v, id, q are kept): QR of <= D normals.
-template <int D, class Rows>
-MPCCBF_HD void gi_rebuild(GIState<D>& g, const Rows& rows) {
-    const int q = g.q;
-    gi_reset_factor<D>(g);
-    g.q = 0;
-#pragma unroll
-    for (int c = 0; c < D; ++c)
-        if (c < q) {
-            double np[D], rhs, d[D];
-            rows.normal(g.id[c], np, rhs);
-            gi_project<D>(g, np, d);
-            gi_add_column<D>(g, d);
-        }
 }
 
 // Rows must provide:
@@ -186,6 +89,12 @@ MPCCBF_HD void gi_rebuild(GIState<D>& g, const Rows& rows) {
 //   double weight(int group) const;     w_j
 //   void set_leader(int group, int id) const;   the piece `id` becomes the leader of its group
 // Returns a SolveStatus code; n_iter is incremented per active-set step.
+//
+// The state carried between steps is only (v, u, ids): every step factorises the <= D active normals
+// afresh (modified Gram-Schmidt, Q R = [n_1 .. n_q]) instead of updating an orthogonal J and a triangular
+// R — with D <= 4 that costs about what the Givens updates did, there is no rounding drift, and the
+// 2 D^2 doubles of J and R are live only inside the step, not across the row scans (which is what kept
+// the thread-per-agent kernel in local memory).
 template <int D, bool SOFT, class Rows>
 __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, int max_iter, int& n_iter) {
     const double kInfD = HUGE_VAL;
@@ -207,31 +116,67 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
         double up_mult = 0.0;
         for (;;) {
             if (++n_iter > max_iter) return MPCCBF_STATUS_ERROR;
-            double d[D];
-            gi_project<D>(g, np, d);
-            // z = J2 d2, |d2|^2, |d|^2
-            double z[D];
+            // ---- Q R = active normals (MGS), d1 = Q' n+, z = n+ - Q d1 ---------------------------------
+            double Q[D][D], R[D][D], d1[D], z[D];
 #pragma unroll
-            for (int i = 0; i < D; ++i) z[i] = 0.0;
-            double ztn = 0.0, dall = 0.0;
+            for (int i = 0; i < D; ++i) z[i] = np[i];
+            double dall = 0.0;
 #pragma unroll
-            for (int j = 0; j < D; ++j) {
-                dall = fma(d[j], d[j], dall);
-                if (j >= g.q) {
-                    ztn = fma(d[j], d[j], ztn);
+            for (int i = 0; i < D; ++i) dall = fma(np[i], np[i], dall);
 #pragma unroll
-                    for (int i = 0; i < D; ++i) z[i] = fma(g.J[i][j], d[j], z[i]);
+            for (int c = 0; c < D; ++c) {
+                d1[c] = 0.0;
+                if (c < g.q) {
+                    double w[D], unused;
+                    rows.normal(g.id[c], w, unused);
+#pragma unroll
+                    for (int p = 0; p < c; ++p) {
+                        double s = 0.0;
+#pragma unroll
+                        for (int i = 0; i < D; ++i) s = fma(Q[i][p], w[i], s);
+                        R[p][c] = s;
+#pragma unroll
+                        for (int i = 0; i < D; ++i) w[i] = fma(-s, Q[i][p], w[i]);
+                    }
+                    double nn = 0.0;
+#pragma unroll
+                    for (int i = 0; i < D; ++i) nn = fma(w[i], w[i], nn);
+                    const double nrm = sqrt(nn), inv = 1.0 / nrm;
+                    R[c][c] = nrm;
+#pragma unroll
+                    for (int i = 0; i < D; ++i) Q[i][c] = w[i] * inv;
+                    // projection of the entering normal (z is already orthogonal to the earlier columns)
+                    double s = 0.0;
+#pragma unroll
+                    for (int i = 0; i < D; ++i) s = fma(Q[i][c], z[i], s);
+                    d1[c] = s;
+#pragma unroll
+                    for (int i = 0; i < D; ++i) z[i] = fma(-s, Q[i][c], z[i]);
                 }
             }
+            // one re-orthogonalisation pass of z (twice is enough)
+#pragma unroll
+            for (int c = 0; c < D; ++c)
+                if (c < g.q) {
+                    double s = 0.0;
+#pragma unroll
+                    for (int i = 0; i < D; ++i) s = fma(Q[i][c], z[i], s);
+                    d1[c] += s;
+#pragma unroll
+                    for (int i = 0; i < D; ++i) z[i] = fma(-s, Q[i][c], z[i]);
+                }
+            double ztn = 0.0;
+#pragma unroll
+            for (int i = 0; i < D; ++i) ztn = fma(z[i], z[i], ztn);
             // r = R^-1 d1
             double rr[D];
 #pragma unroll
             for (int i = D - 1; i >= 0; --i) {
-                double s = d[i];
+                double s = d1[i];
 #pragma unroll
                 for (int k = i + 1; k < D; ++k)
-                    if (k < g.q) s = fma(-g.Rm[i][k], rr[k], s);
-                rr[i] = (i < g.q) ? s / g.Rm[i][i] : 0.0;
+                    if (k < g.q) s = fma(-R[i][k], rr[k], s);
+                rr[i] = (i < g.q) ? s / R[i][i] : 0.0;
             }
             const double zt = 1e4 * 2.220446049250313e-16;
             const bool z_zero = !(ztn > zt * zt * dall);
@@ -254,7 +199,7 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
             double t3 = kInfD;
             int g3 = -1;
             if constexpr (SOFT) {
-                // entries: the entering row (rate +1, multiplier up_mult) and the active columns (rate -rr)
+                // entries: the entering row (rate +1, multiplier up_mult) and the active rows (rate -rr)
 #pragma unroll
                 for (int e = -1; e < D; ++e) {
                     const int ge = (e < 0) ? pgrp : ((e < g.q) ? gs.grp[e] : -1);
@@ -293,7 +238,7 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
             up_mult += t;
 
             if (!z_zero && t2 <= t1 && t2 <= t3) {
-                // full step: add the row
+                // full step: the row joins the active set
 #pragma unroll
                 for (int col = 0; col < D; ++col)
                     if (col == g.q) {
@@ -304,7 +249,7 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
                             gs.cap[col] = pcap;
                         }
                     }
-                gi_add_column<D>(g, d);
+                ++g.q;
                 break;
             }
             if constexpr (SOFT) if (t3 <= t1) {
@@ -327,33 +272,14 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
                 for (int c = 0; c < D; ++c)
                     if (c == a) aid = g.id[c];
                 rows.set_leader(g3, aid);
-#pragma unroll
-                for (int c = 0; c < D - 1; ++c)
-                    if (c >= a) {
-                        g.u[c] = g.u[c + 1];
-                        g.id[c] = g.id[c + 1];
-                        gs.grp[c] = gs.grp[c + 1];
-                        gs.cap[c] = gs.cap[c + 1];
-                    }
-                g.u[D - 1] = 0.0;
-                g.id[D - 1] = -1;
-                gs.grp[D - 1] = -1;
-                --g.q;
-                gi_rebuild<D>(g, rows);  // the group's other active rows are now expressed against the new leader
+                gi_remove<D, true>(g, gs, a);   // its multiplier is implicit from now on
+                // (the group's other active rows and, if it belongs to g3, the entering row are expressed against
+                // the new leader from here on: normal() reads the leader)
                 if (pgrp == g3) rows.normal(best_id, np, rhs);
                 continue;
             }
-            // partial (or dual-only) step: drop active row lpos
-            if constexpr (SOFT) {
-#pragma unroll
-                for (int c = 0; c < D - 1; ++c)
-                    if (c >= lpos) {
-                        gs.grp[c] = gs.grp[c + 1];
-                        gs.cap[c] = gs.cap[c + 1];
-                    }
-                gs.grp[D - 1] = -1;
-            }
-            gi_drop_column<D>(g, lpos);
+            // partial (or dual-only) step: active row lpos leaves
+            gi_remove<D, SOFT>(g, gs, lpos);
         }
     }
 }

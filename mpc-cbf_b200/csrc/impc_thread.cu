@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -30,7 +31,8 @@ namespace mpccbf {
 #define MPCCBF_THREAD_MIN_CTAS 4
 #endif
 constexpr int kCandMax = 32;   // candidate safety rows kept per agent (more: scan all rows)
-constexpr int kSolStride = 13; // per-agent result record: s[6] (pos xyz, vel xyz), v[6], n_ok
+constexpr int kSolStride = 7;  // per-agent result record: v[6] (whitened free dof of the last successful iterate), n_ok
+constexpr int kSnapD = 8, kSnapI = 5;  // stage-A snapshot per agent: v[4], u[4] | id[4], q
 
 #ifdef __CUDA_ARCH__
 #define TLDG(p) __ldg(p)
@@ -139,7 +141,7 @@ MPCCBF_HD void scan_axis_keys(const double* scn, int K, float kinv, const AxisPo
 // both x/y axes: key[ax * 2 + dsel]
 MPCCBF_HD void scan_axes_keys2(const double* scn, int K, float kinv, const AxisPoly& ax, const AxisPoly& ay, const double* lim, int (&key)[4]) {
     scan_axis_keys(scn, K, kinv, ax, lim[0], lim[1], lim[2], lim[3], key[0], key[1]);
-    scan_axis_keys(scn, K, kinv, ay, lim[4], lim[5], lim[6], lim[7], key[2], key[3]);
+    scan_axis_keys(scn, K, kinv, ay, lim[8], lim[9], lim[10], lim[11], key[2], key[3]);
 }
 MPCCBF_HD double bound_hi_eff(double hi, double tol) { return fabs(hi) < 1e20 ? hi + tol * fmax(1.0, fabs(hi)) : HUGE_VAL; }
 MPCCBF_HD double bound_lo_eff(double lo, double tol) { return fabs(lo) < 1e20 ? lo - tol * fmax(1.0, fabs(lo)) : -HUGE_VAL; }
@@ -149,12 +151,11 @@ struct RowsAxis {
     const double* tm;  // templates [3][K][kTmplStride]
     int K;
     double s0, s1;       // own pos, vel on this axis
-    double lo[2], hi[2]; // [0] acceleration rows, [1] velocity rows
     double tol;
     const double (*pq)[4];  // polynomial row structure (DevTables::poly)
     const double* scn;      // [K][4] key-scan table
     float kinv;             // (K - 1) / t_{K-1}
-    const double* lim;      // {midA, halfA, midV, halfV} of this axis
+    const double* lim;      // this axis: {midA, halfA, midV, halfV, loA, hiA, loV, hiV} (mid / half of the thresholded bounds)
 
     MPCCBF_HD void scan(const double (&v)[2], double& best, int& best_id) const {
         const AxisPoly a = axis_poly(pq, v[0], v[1], s0, s1);
@@ -168,7 +169,7 @@ struct RowsAxis {
         // which side of the winning row is violated
         const double* t = tm + ((2 - dsel) * K + k) * kTmplStride;
         const double val = fma(t[0], v[0], fma(t[1], v[1], fma(t[2], s0, t[3] * s1)));
-        if (val - hi[dsel] > lo[dsel] - val) best_id |= 1;
+        if (val - lim[5 + 2 * dsel] > lim[4 + 2 * dsel] - val) best_id |= 1;
     }
     MPCCBF_HD void normal(int id, double (&np)[2], double& rhs) const {
         const bool up = id & 1;
@@ -177,7 +178,7 @@ struct RowsAxis {
         const int k = r - dsel * K;
         const double* t = tm + ((2 - dsel) * K + k) * kTmplStride;
         const double sg = up ? -1.0 : 1.0;
-        const double bound = up ? (dsel ? hi[1] : hi[0]) : (dsel ? lo[1] : lo[0]);
+        const double bound = lim[4 + 2 * dsel + (up ? 1 : 0)];
         np[0] = sg * t[0];
         np[1] = sg * t[1];
         rhs = sg * (bound - fma(t[2], s0, t[3] * s1));
@@ -221,7 +222,6 @@ struct RowsXY {
     const double* tm;
     int K;
     double s[2][2];       // [axis][pos, vel]
-    double lo[2][2], hi[2][2];  // [dsel][axis]
     double tol;
     // safety rows
     const double* st;     // scenario states (shared memory) [N][6]
@@ -235,7 +235,7 @@ struct RowsXY {
     const double (*pq)[4];  // polynomial row structure (DevTables::poly)
     const double* scn;      // [K][4] key-scan table
     float kinv;             // (K - 1) / t_{K-1}
-    const double* lim;      // [axis x, y]{midA, halfA, midV, halfV}
+    const double* lim;      // [axis x, y][8] = {midA, halfA, midV, halfV, loA, hiA, loV, hiV}
     // slack mode
     unsigned char* lead;  // [N-1] leaders of this agent's groups
     int nnb;              // N - 1
@@ -336,9 +336,8 @@ struct RowsXY {
         const double va = ax ? v[2] : v[0], vb = ax ? v[3] : v[1];
         const double sa = ax ? s[1][0] : s[0][0], sb = ax ? s[1][1] : s[0][1];
         const double val = fma(t[0], va, fma(t[1], vb, fma(t[2], sa, t[3] * sb)));
-        const double l = dsel ? (ax ? lo[1][1] : lo[1][0]) : (ax ? lo[0][1] : lo[0][0]);
-        const double h = dsel ? (ax ? hi[1][1] : hi[1][0]) : (ax ? hi[0][1] : hi[0][0]);
-        if (val - h > l - val) best_id |= 1;
+        const double* lm = lim + 8 * ax + 4 + 2 * dsel;
+        if (val - lm[1] > lm[0] - val) best_id |= 1;
     }
     // sg * (normal, rhs) of safety row j accumulated into (np, rhs)
     MPCCBF_HD void add_cbf_normal(int j, double sg, double (&np)[4], double& rhs) const {
@@ -364,9 +363,7 @@ struct RowsXY {
             const int k = dk - dsel * K;
             const double* t = tm + ((2 - dsel) * K + k) * kTmplStride;
             const double sg = up ? -1.0 : 1.0;
-            const double bhi = dsel ? (ax ? hi[1][1] : hi[1][0]) : (ax ? hi[0][1] : hi[0][0]);
-            const double blo = dsel ? (ax ? lo[1][1] : lo[1][0]) : (ax ? lo[0][1] : lo[0][0]);
-            const double bound = up ? bhi : blo;
+            const double bound = lim[8 * ax + 4 + 2 * dsel + (up ? 1 : 0)];
             const double sa = ax ? s[1][0] : s[0][0], sb = ax ? s[1][1] : s[0][1];
             const double n0 = sg * t[0], n1 = sg * t[1];
             np[0] = ax ? 0.0 : n0;
@@ -414,12 +411,15 @@ struct AgentCtx {
     const double *tm, *yw, *vr, *kr;  // constant tables (shared memory on the device)
     const double (*pq)[4];            // polynomial row structure (DevTables::poly)
     const double* scn;                // [K][4] key-scan table {t_k, inv_norm_acc, inv_norm_vel, -}
-    const double* lim;                // [3 axes]{midA, halfA, midV, halfV} of the thresholded bounds
+    const double* lim;                // [3 axes][8]: mid / half of the thresholded bounds, raw lo / hi
     const double* st;                 // this agent's scenario states [N][6]
     double* pred;                     // [(k*4 + c) * pstride]
     unsigned short* cand;             // [i * cstride]
     int pstride, cstride;
     double* sol;                      // [kSolStride] result record of this agent
+    double* snapd;                    // [kSnapD * sstride] stage-A snapshot (doubles), snapi (ints)
+    int* snapi;
+    int sstride;
     unsigned char* lead;              // [N-1] group leaders of this agent (slack mode), else NULL
 };
 
@@ -443,11 +443,19 @@ MPCCBF_HD void build_candidates(RowsXY<SOFT>& rx, const DevTables& T, unsigned s
     rx.ncand = (wide || nc > kCandMax) ? -1 : nc;
 }
 
-MPCCBF_HD double ctrl_point(const double* y, int ax, const double* sol) {
+MPCCBF_HD double ctrl_point(const double* y, double ps, double vs, double va, double vb) {
     // x[piece, ax, cp] = Y1 (pos, vel) + W1 (va, vb)
     // (explicit fma chain: mpccbf_expand_ctrl_pts evaluates the same expression on the host, bit for bit)
-    return fma(y[0], sol[ax], fma(y[1], sol[3 + ax], fma(y[2], sol[6 + 2 * ax], y[3] * sol[7 + 2 * ax])));
+    return fma(y[0], ps, fma(y[1], vs, fma(y[2], va, y[3] * vb)));
 }
+
+// Unconstrained minimiser v0 (whitened coordinates) and, when WANT_C0, the constant part c0 of the objective.
+// Evaluated twice per agent (before the solves, and again for the objective value at the end) instead of
+// keeping v0 live across the active-set iterations.
+struct AgentCtx;
+template <bool WANT_C0>
+MPCCBF_HD void unconstrained_minimiser(const DevTables& T, const StepArgs& a, int g, const double (&s)[3][2], const AgentCtx& c,
+                                       double (&v0)[6], double& c0);
 
 // Everything optimize() does for agent-QP g (one thread).
 template <bool SOFT>
@@ -459,36 +467,10 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         s[ax][0] = c.st[self * 6 + ax];
         s[ax][1] = c.st[self * 6 + 3 + ax];
     }
-    // ---- unconstrained minimiser (whitened) and constant objective part ----------------------
-    double v0[6], c0 = 0.0;
-    if (a.ref_mode == 0) {
-        const double* tg = a.targets + static_cast<size_t>(g) * 3;
-#pragma unroll
-        for (int ax = 0; ax < 3; ++ax) {
-            const double tgt = TLDG(tg + ax);
-            const double ps = s[ax][0], vs = s[ax][1];
-            v0[2 * ax] = T.Vs[0][0] * ps + T.Vs[0][1] * vs + T.Vt[0] * tgt;
-            v0[2 * ax + 1] = T.Vs[1][0] * ps + T.Vs[1][1] * vs + T.Vt[1] * tgt;
-            c0 += ps * (T.Kc[0][0] * ps + T.Kc[0][1] * vs) + vs * (T.Kc[1][0] * ps + T.Kc[1][1] * vs) +
-                  tgt * (T.Kt[0] * ps + T.Kt[1] * vs);
-        }
-    } else {
-        const double* rf = a.targets + static_cast<size_t>(g) * 3 * K;
-#pragma unroll
-        for (int ax = 0; ax < 3; ++ax) {
-            const double ps = s[ax][0], vs = s[ax][1];
-            double r0 = 0.0, r1 = 0.0, k0 = 0.0, k1 = 0.0;
-            for (int k = 0; k < K; ++k) {
-                const double rk = TLDG(rf + 3 * k + ax);
-                r0 = fma(c.vr[k], rk, r0);
-                r1 = fma(c.vr[K + k], rk, r1);
-                k0 = fma(c.kr[k], rk, k0);
-                k1 = fma(c.kr[K + k], rk, k1);
-            }
-            v0[2 * ax] = T.Vs[0][0] * ps + T.Vs[0][1] * vs + r0;
-            v0[2 * ax + 1] = T.Vs[1][0] * ps + T.Vs[1][1] * vs + r1;
-            c0 += ps * (T.Kc[0][0] * ps + T.Kc[0][1] * vs) + vs * (T.Kc[1][0] * ps + T.Kc[1][1] * vs) + (k0 * ps + k1 * vs);
-        }
+    double v0[6];
+    {
+        double c0_unused;
+        unconstrained_minimiser<false>(T, a, g, s, c, v0, c0_unused);
     }
     const float kinv = static_cast<float>((K - 1) / c.scn[4 * (K - 1)]);
     int total_iter = 0;
@@ -502,13 +484,11 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         ry.K = K;
         ry.s0 = s[2][0];
         ry.s1 = s[2][1];
-        ry.lo[0] = T.lim_lo[0][2]; ry.hi[0] = T.lim_hi[0][2];
-        ry.lo[1] = T.lim_lo[1][2]; ry.hi[1] = T.lim_hi[1][2];
         ry.tol = T.feas_tol;
         ry.pq = c.pq;
         ry.scn = c.scn;
         ry.kinv = kinv;
-        ry.lim = c.lim + 8;
+        ry.lim = c.lim + 16;
         base_status = gi_run<2>(gy, ry, T.max_gi, total_iter);
     }
     // ---- x/y stage A: bound rows only ---------------------------------------------------------
@@ -519,11 +499,6 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     for (int ax = 0; ax < 2; ++ax) {
         rx.s[ax][0] = s[ax][0];
         rx.s[ax][1] = s[ax][1];
-#pragma unroll
-        for (int d = 0; d < 2; ++d) {
-            rx.lo[d][ax] = T.lim_lo[d][ax];
-            rx.hi[d][ax] = T.lim_hi[d][ax];
-        }
     }
     rx.tol = T.feas_tol;
     rx.st = c.st;
@@ -556,8 +531,6 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     gi_init<4>(gx, v0);
     // stage-A solution: iterate, multipliers and ids of its active bound rows (the factorisation is
     // rebuilt from the ids when a later IMPC iteration has to start from it again)
-    double snap_v[4], snap_u[4];
-    int snap_id[4], snap_q = 0;
 
     // Phase machine with ONE gi_run<4> call site (the unrolled 4-dof active-set code is the bulk of
     // the kernel's instruction footprint; inlining it once keeps the kernel inside the instruction
@@ -566,7 +539,6 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     enum { kStageA = 0, kIter = 2 };
     int n_ok = 0;
     bool dirty = false;  // gx has safety rows in its active set (not reusable as stage A)
-    double vlast[6] = {0, 0, 0, 0, 0, 0};
     double pen_last = 0.0;  // slack mode: sum_j w_j s_j of the last successful iterate
     const size_t sbase = static_cast<size_t>(g) * T.iters;
     int mode = kStageA, it = 0, it_iter = 0;
@@ -598,13 +570,12 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                 if (dirty) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        gx.v[i] = snap_v[i];
-                        gx.u[i] = snap_u[i];
-                        gx.id[i] = snap_id[i];
+                        gx.v[i] = c.snapd[i * c.sstride];
+                        gx.u[i] = c.snapd[(4 + i) * c.sstride];
+                        gx.id[i] = c.snapi[i * c.sstride];
                         if constexpr (SOFT) gs.grp[i] = -1;
                     }
-                    gx.q = snap_q;
-                    gi_rebuild<4>(gx, rx);
+                    gx.q = c.snapi[4 * c.sstride];
                 }
                 dirty = false;
                 rx.hit = hit;
@@ -625,11 +596,11 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
             it_iter += total_iter;  // yaw iterations are booked on IMPC iteration 0
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                snap_v[i] = gx.v[i];
-                snap_u[i] = gx.u[i];
-                snap_id[i] = gx.id[i];
+                c.snapd[i * c.sstride] = gx.v[i];
+                c.snapd[(4 + i) * c.sstride] = gx.u[i];
+                c.snapi[i * c.sstride] = gx.id[i];
             }
-            snap_q = gx.q;
+            c.snapi[4 * c.sstride] = gx.q;
             mode = kIter;
             continue;
         }
@@ -646,44 +617,36 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         }
         ++n_ok;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) vlast[i] = gx.v[i];
-        vlast[4] = gy.v[0];
-        vlast[5] = gy.v[1];
+        for (int i = 0; i < 4; ++i) c.sol[i] = gx.v[i];
+        c.sol[4] = gy.v[0];
+        c.sol[5] = gy.v[1];
         if constexpr (SOFT) pen_last = (run && a.objective) ? rx.penalty(gx.v) : 0.0;
         if (a.ctrl_all) {  // every iterate (mpccbf_optimize_one): small batches, direct stores
-#pragma unroll
-            for (int ax = 0; ax < 3; ++ax) {
-                c.sol[ax] = s[ax][0];
-                c.sol[3 + ax] = s[ax][1];
-            }
-#pragma unroll
-            for (int i = 0; i < 6; ++i) c.sol[6 + i] = vlast[i];
             double* out = a.ctrl_all + (sbase + it) * T.n;
             for (int i = 0; i < T.n; ++i) {
                 const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
                 const int ax = rem / T.c, cp = rem - ax * T.c;
-                out[i] = ctrl_point(c.yw + (piece * T.c + cp) * 4, ax, c.sol);
+                out[i] = ctrl_point(c.yw + (piece * T.c + cp) * 4, c.st[self * 6 + ax], c.st[self * 6 + 3 + ax], c.sol[2 * ax], c.sol[2 * ax + 1]);
             }
         }
         ++it;
     }
     // ---- result record (expanded to control points cooperatively by the warp) ------------------
+    if (n_ok == 0) {
 #pragma unroll
-    for (int ax = 0; ax < 3; ++ax) {
-        c.sol[ax] = s[ax][0];
-        c.sol[3 + ax] = s[ax][1];
+        for (int i = 0; i < 6; ++i) c.sol[i] = 0.0;
     }
-#pragma unroll
-    for (int i = 0; i < 6; ++i) c.sol[6 + i] = vlast[i];
-    c.sol[12] = static_cast<double>(n_ok);
+    c.sol[6] = static_cast<double>(n_ok);
     if (a.n_curves) a.n_curves[g] = n_ok;
     if (a.objective) {
         double obj = 0.0;
         if (n_ok > 0) {
+            double c0;
+            unconstrained_minimiser<true>(T, a, g, s, c, v0, c0);
             double dd = 0.0, nn = 0.0;
 #pragma unroll
             for (int i = 0; i < 6; ++i) {
-                const double e = vlast[i] - v0[i];
+                const double e = c.sol[i] - v0[i];
                 dd = fma(e, e, dd);
                 nn = fma(v0[i], v0[i], nn);
             }
@@ -693,14 +656,55 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     }
 }
 
-// lim[axis] = {midA, halfA, midV, halfV} of the thresholded bounds; scn[k] = {t_k, inv_norm of the
+template <bool WANT_C0>
+MPCCBF_HD void unconstrained_minimiser(const DevTables& T, const StepArgs& a, int g, const double (&s)[3][2], const AgentCtx& c,
+                                       double (&v0)[6], double& c0) {
+    const int K = T.K;
+    c0 = 0.0;
+    if (a.ref_mode == 0) {
+        const double* tg = a.targets + static_cast<size_t>(g) * 3;
+#pragma unroll
+        for (int ax = 0; ax < 3; ++ax) {
+            const double tgt = TLDG(tg + ax);
+            const double ps = s[ax][0], vs = s[ax][1];
+            v0[2 * ax] = T.Vs[0][0] * ps + T.Vs[0][1] * vs + T.Vt[0] * tgt;
+            v0[2 * ax + 1] = T.Vs[1][0] * ps + T.Vs[1][1] * vs + T.Vt[1] * tgt;
+            if (WANT_C0)
+                c0 += ps * (T.Kc[0][0] * ps + T.Kc[0][1] * vs) + vs * (T.Kc[1][0] * ps + T.Kc[1][1] * vs) +
+                      tgt * (T.Kt[0] * ps + T.Kt[1] * vs);
+        }
+    } else {
+        const double* rf = a.targets + static_cast<size_t>(g) * 3 * K;
+#pragma unroll
+        for (int ax = 0; ax < 3; ++ax) {
+            const double ps = s[ax][0], vs = s[ax][1];
+            double r0 = 0.0, r1 = 0.0, k0 = 0.0, k1 = 0.0;
+            for (int k = 0; k < K; ++k) {
+                const double rk = TLDG(rf + 3 * k + ax);
+                r0 = fma(c.vr[k], rk, r0);
+                r1 = fma(c.vr[K + k], rk, r1);
+                if (WANT_C0) {
+                    k0 = fma(c.kr[k], rk, k0);
+                    k1 = fma(c.kr[K + k], rk, k1);
+                }
+            }
+            v0[2 * ax] = T.Vs[0][0] * ps + T.Vs[0][1] * vs + r0;
+            v0[2 * ax + 1] = T.Vs[1][0] * ps + T.Vs[1][1] * vs + r1;
+            if (WANT_C0) c0 += ps * (T.Kc[0][0] * ps + T.Kc[0][1] * vs) + vs * (T.Kc[1][0] * ps + T.Kc[1][1] * vs) + (k0 * ps + k1 * vs);
+        }
+    }
+}
+
+// lim[axis] = {midA, halfA, midV, halfV (of the thresholded bounds), loA, hiA, loV, hiV}; scn[k] = {t_k, inv_norm of the
 // acceleration row, inv_norm of the velocity row, 0} with 1e300 standing for "row independent of v"
 __host__ __device__ inline void fill_scan_tables(const DevTables& T, const double* tm, double* lim, double* scn, int tid, int nthr) {
     for (int i = tid; i < 6; i += nthr) {
         const int axis = i >> 1, dsel = i & 1;
         const double hi = bound_hi_eff(T.lim_hi[dsel][axis], T.feas_tol), lo = bound_lo_eff(T.lim_lo[dsel][axis], T.feas_tol);
-        lim[axis * 4 + dsel * 2 + 0] = 0.5 * (hi + lo);
-        lim[axis * 4 + dsel * 2 + 1] = 0.5 * (hi - lo);
+        lim[axis * 8 + dsel * 2 + 0] = 0.5 * (hi + lo);
+        lim[axis * 8 + dsel * 2 + 1] = 0.5 * (hi - lo);
+        lim[axis * 8 + 4 + dsel * 2 + 0] = T.lim_lo[dsel][axis];
+        lim[axis * 8 + 4 + dsel * 2 + 1] = T.lim_hi[dsel][axis];
     }
     for (int k = tid; k < T.K; k += nthr) {
         scn[4 * k + 0] = tm[(2 * T.K + k) * kTmplStride + 5];
@@ -712,7 +716,7 @@ __host__ __device__ inline void fill_scan_tables(const DevTables& T, const doubl
 
 struct ThreadSmemLayout {
     int tm, yw, vr, kr, vq, omap_bytes;  // doubles (omap in bytes), CTA-shared
-    int st, pred, sol, cand_bytes;   // per warp: doubles (cand in bytes)
+    int st, pred, sol, snapd, snapi_bytes, cand_bytes;   // per warp: doubles (snapi, cand in bytes)
     int nscen_max;
     size_t shared_bytes, warp_bytes;
 };
@@ -723,20 +727,23 @@ static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count) {
     L.yw = T.m1 * 4;
     L.vr = 2 * T.K;
     L.kr = 2 * T.K;
-    L.vq = 20 + 12 + 4 * T.K;  // pq, lim[3][4], scn[K][4]
+    L.vq = 20 + 24 + 4 * T.K;  // pq, lim[3][8], scn[K][4]
     L.omap_bytes = ((T.n * 2 + 15) / 16) * 16;
     L.nscen_max = (32 - 1) / std::max(agent_count, 1) + 2;
     L.st = L.nscen_max * T.N * 6;
     L.pred = std::max(T.H, 1) * 4 * 32;
     L.sol = 32 * kSolStride;
+    L.snapd = 32 * kSnapD;
+    L.snapi_bytes = 32 * kSnapI * 4;
     L.cand_bytes = kCandMax * 32 * 2;
     L.shared_bytes = sizeof(double) * (L.tm + L.yw + L.vr + L.kr + L.vq) + L.omap_bytes;
-    L.warp_bytes = sizeof(double) * (L.st + L.pred + L.sol) + L.cand_bytes;
+    L.warp_bytes = sizeof(double) * (L.st + L.pred + L.sol + L.snapd) + L.snapi_bytes + L.cand_bytes;
     return L;
 }
 
-template <bool SOFT>
-__global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kernel(const DevTables T, const StepArgs a, const ThreadSmemLayout L) {
+template <bool SOFT, int MIN_CTAS>
+__global__ void __launch_bounds__(128, MIN_CTAS)
+impc_thread_kernel(const __grid_constant__ DevTables T, const __grid_constant__ StepArgs a, const __grid_constant__ ThreadSmemLayout L) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* tm = reinterpret_cast<double*>(smem_raw);
     double* yw = tm + L.tm;
@@ -748,7 +755,9 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
     double* wst = reinterpret_cast<double*>(wbase);
     double* wpred = wst + L.st;
     double* wsol = wpred + L.pred;
-    unsigned short* wcand = reinterpret_cast<unsigned short*>(wsol + L.sol);
+    double* wsnapd = wsol + L.sol;
+    int* wsnapi = reinterpret_cast<int*>(wsnapd + L.snapd);
+    unsigned short* wcand = reinterpret_cast<unsigned short*>(reinterpret_cast<unsigned char*>(wsnapi) + L.snapi_bytes);
 
     for (int i = threadIdx.x; i < L.tm; i += blockDim.x) tm[i] = T.tmpl[i];
     for (int i = threadIdx.x; i < L.yw; i += blockDim.x) yw[i] = T.yw[i];
@@ -757,7 +766,7 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
         kr[i] = T.Kr[i];
     }
     if (threadIdx.x < 20) svq[threadIdx.x] = T.pq[threadIdx.x >> 2][threadIdx.x & 3];
-    fill_scan_tables(T, tm, svq + 20, svq + 32, threadIdx.x, blockDim.x);
+    fill_scan_tables(T, tm, svq + 20, svq + 44, threadIdx.x, blockDim.x);
     for (int i = threadIdx.x; i < T.n; i += blockDim.x) {
         const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
         const int ax = rem / T.c, cp = rem - ax * T.c;
@@ -792,13 +801,16 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
             c.tm = tm; c.yw = yw; c.vr = vr; c.kr = kr;
             c.pq = reinterpret_cast<const double (*)[4]>(svq);
             c.lim = svq + 20;
-            c.scn = svq + 32;
+            c.scn = svq + 44;
             c.st = wst + (scen - s_lo) * N * 6;
             c.pred = wpred + lane;
             c.pstride = 32;
             c.cand = wcand + lane;
             c.cstride = 32;
             c.sol = wsol + lane * kSolStride;
+            c.snapd = wsnapd + lane;
+            c.snapi = wsnapi + lane;
+            c.sstride = 32;
             c.lead = SOFT ? a.lead_ws + static_cast<size_t>(g) * (N - 1) : nullptr;
             agent_thread<SOFT>(T, a, g, self, c);
         }
@@ -807,8 +819,7 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
             double* vo = a.v_out + static_cast<size_t>(g0) * 6;
             for (int idx = lane; idx < cnt * 6; idx += 32) {
                 const int ag = idx / 6, i = idx - ag * 6;
-                const double* rec = wsol + ag * kSolStride;
-                vo[idx] = (rec[12] > 0.0) ? rec[6 + i] : 0.0;
+                vo[idx] = wsol[ag * kSolStride + i];   // zeros when the agent has no curve
             }
         }
         if (a.ctrl_pts) {   // control points of the last successful iterate: coalesced stores, whole warp
@@ -817,8 +828,11 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
             for (int idx = lane; idx < total; idx += 32) {
                 const int ag = idx / n, i = idx - ag * n;
                 const double* rec = wsol + ag * kSolStride;
+                const int gg = g0 + ag, sc = gg / a.agent_count;
+                const double* sta = wst + ((sc - s_lo) * N + a.agent_begin + (gg - sc * a.agent_count)) * 6;
                 const unsigned m = omap[i];
-                out[idx] = (rec[12] > 0.0) ? ctrl_point(yw + (m >> 2) * 4, m & 3, rec) : 0.0;
+                const int ax = m & 3;
+                out[idx] = (rec[6] > 0.0) ? ctrl_point(yw + (m >> 2) * 4, sta[ax], sta[3 + ax], rec[2 * ax], rec[2 * ax + 1]) : 0.0;
             }
         }
         __syncwarp();
@@ -830,7 +844,9 @@ __global__ void __launch_bounds__(128, MPCCBF_THREAD_MIN_CTAS) impc_thread_kerne
 void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
     std::vector<double> pred(static_cast<size_t>(std::max(T.H, 1)) * 4), sol(kSolStride);
     std::vector<unsigned short> cand(kCandMax);
-    std::vector<double> lim(12), scn(static_cast<size_t>(4) * T.K);
+    std::vector<double> snapd(kSnapD);
+    std::vector<int> snapi(kSnapI);
+    std::vector<double> lim(24), scn(static_cast<size_t>(4) * T.K);
     std::vector<unsigned char> lead(static_cast<size_t>(std::max(T.N, 1)));
     fill_scan_tables(T, T.tmpl, lim.data(), scn.data(), 0, 1);
     for (int g = 0; g < a.num_qp; ++g) {
@@ -847,18 +863,21 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
         c.cand = cand.data();
         c.cstride = 1;
         c.sol = sol.data();
+        c.snapd = snapd.data();
+        c.snapi = snapi.data();
+        c.sstride = 1;
         c.lead = lead.data();
         if (T.slack)
             agent_thread<true>(T, a, g, self, c);
         else
             agent_thread<false>(T, a, g, self, c);
         if (a.v_out)
-            for (int i = 0; i < 6; ++i) a.v_out[static_cast<size_t>(g) * 6 + i] = (sol[12] > 0.0) ? sol[6 + i] : 0.0;
+            for (int i = 0; i < 6; ++i) a.v_out[static_cast<size_t>(g) * 6 + i] = sol[i];
         double* out = a.ctrl_pts + static_cast<size_t>(g) * T.n;
         for (int i = 0; a.ctrl_pts && i < T.n; ++i) {
             const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
             const int ax = rem / T.c, cp = rem - ax * T.c;
-            out[i] = (sol[12] > 0.0) ? ctrl_point(T.yw + (piece * T.c + cp) * 4, ax, sol.data()) : 0.0;
+            out[i] = (sol[6] > 0.0) ? ctrl_point(T.yw + (piece * T.c + cp) * 4, c.st[self * 6 + ax], c.st[self * 6 + 3 + ax], sol[2 * ax], sol[2 * ax + 1]) : 0.0;
         }
     }
 }
@@ -876,7 +895,16 @@ int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cuda
     }
     if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
     if (T.slack && !a.lead_ws) return cudaErrorInvalidValue;
-    auto kern = T.slack ? impc_thread_kernel<true> : impc_thread_kernel<false>;
+    // register budget per thread: 128 (4 CTAs of 128 threads per SM), 168 (3) or 255 (2). MPCCBF_THREAD_CTAS overrides
+    // the default for experiments (profiles/r2*_occupancy.md has the measured comparison).
+    static const int ctas = [] {
+        const char* e = std::getenv("MPCCBF_THREAD_CTAS");
+        const int v = e ? std::atoi(e) : MPCCBF_THREAD_MIN_CTAS;
+        return (v == 2 || v == 3) ? v : 4;
+    }();
+    auto kern = T.slack ? impc_thread_kernel<true, 4> : impc_thread_kernel<false, 4>;
+    if (ctas == 3) kern = T.slack ? impc_thread_kernel<true, 3> : impc_thread_kernel<false, 3>;
+    if (ctas == 2) kern = T.slack ? impc_thread_kernel<true, 2> : impc_thread_kernel<false, 2>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return e;
     int per_sm = 1;
