@@ -93,6 +93,12 @@ typedef struct mpccbf_config {
     double admm_eps;          /* abs = rel termination tolerance, default 1e-7          */
     double admm_rho;          /* initial rho, default 0.1                               */
     double admm_sigma;        /* default 1e-6                                           */
+    int32_t conn_mode;        /* 0 (the reference as shipped: the block is commented out,
+                               * ConnectivityIMPCCBF.cpp:143-157,177-192) or 1: lambda2 > 0.1 ->
+                               * the MPC-lifted connectivity HOCBF row at every CBF horizon step,
+                               * else one distance-CLF row per neighbour and step
+                               * (ConnectivityMPCCBFQPOperations.cpp:45-86,111-173). Needs
+                               * num_agents <= 32 and slack_mode = 0                        */
 } mpccbf_config;
 
 typedef struct mpccbf_handle mpccbf_handle;

@@ -49,6 +49,9 @@ struct mpccbf_handle {
     // slack mode (cbf_params.slack_mode): capped multipliers inside the fused thread-per-agent kernel
     // (gi_solver.h); scratch = one leader byte per (agent, neighbour)
     unsigned char* w_lead = nullptr;
+    // conn_mode: lambda2 [S] and Fiedler vector [S][N] of every scenario (cbf_filter.cu), refreshed before every step
+    double *w_lam2 = nullptr, *w_fied = nullptr;
+    std::vector<double> hc_lam2, hc_fied;  // host-only handles (tests/emul)
     int64_t launches = 0, qps = 0;
 };
 
@@ -106,6 +109,8 @@ int build_device_tables(mpccbf_handle* h) {
     d.slack = h->cfg.slack_mode ? 1 : 0;
     d.slack_cost = h->cfg.slack_cost;
     d.slack_decay = h->cfg.slack_decay;
+    d.conn_mode = h->cfg.conn_mode ? 1 : 0;
+    d.dmax = h->cfg.d_max;
     // rollout constants: t = h with the reference's lower_bound piece rule
     {
         RolloutConst& rc = h->rc;
@@ -299,7 +304,7 @@ int resolve_lanes(const mpccbf_handle* h, int64_t num_qp, bool force_auto = fals
         const int wave = 8 * h->sm_count * (h->cfg.num_agents >= 128 ? 2 : 1);
         lanes = (num_qp <= wave) ? 32 : 0;
     }
-    if (h->cfg.slack_mode) lanes = 0;  // capped multipliers live in the thread-per-agent kernel only
+    if (h->cfg.slack_mode || h->cfg.conn_mode) lanes = 0;  // capped multipliers / lifted connectivity rows: thread-per-agent kernel only
     if (lanes == 0 && !h->dev.poly)  // the thread kernel needs the polynomial row structure
         lanes = (num_qp >= 2048 && h->cfg.num_agents < 64) ? 8 : 32;
     return lanes;
@@ -328,6 +333,12 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
     a.lead_ws = h->w_lead;
+    if (h->cfg.conn_mode) {  // one warp per scenario: Laplacian, Jacobi eigen-solve, second smallest eigenpair
+        CUDA_TRY(launch_cbf_filter(h->cfg, S, states, nullptr, nullptr, nullptr, h->w_lam2, nullptr, h->sm_count, stream, h->w_fied));
+        a.lambda2 = h->w_lam2;
+        a.fiedler = h->w_fied;
+        h->launches += 1;
+    }
     const int lanes = resolve_lanes(h, a.num_qp);
     if (lanes == 0)
         CUDA_TRY(launch_impc_thread(h->dev, a, h->sm_count, stream));
@@ -422,6 +433,13 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
         mpccbf_destroy(h);
         return rc;
     }
+    if (h->cfg.conn_mode && (h->cfg.slack_mode || h->cfg.num_agents > 32 || h->solver != MPCCBF_SOLVER_REDUCED || !h->dev.poly)) {
+        set_error("conn_mode needs slack_mode = 0 (the reference indexes the slack of the connectivity row by self_idx, out of "
+                  "range for the last robot: ConnectivityMPCCBFQPGenerator.cpp:56-58), num_agents <= 32 (one lane per agent in "
+                  "the eigen-solve) and a configuration the thread-per-agent kernel serves");
+        mpccbf_destroy(h);
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
     if (h->cfg.slack_mode && h->solver == MPCCBF_SOLVER_REDUCED && !h->dev.poly) {
         set_error("slack mode needs the polynomial row structure of the thread-per-agent kernel (k_hor in 4..127, finite "
                   "velocity and acceleration limits)");
@@ -444,6 +462,10 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
         ok &= cudaMalloc(&h->o_ctrl, sizeof(double) * n) == cudaSuccess;
         ok &= cudaMalloc(&h->o_all, sizeof(double) * n * it) == cudaSuccess;
         ok &= cudaMalloc(&h->o_status, sizeof(int32_t) * (it + 1 + it)) == cudaSuccess;
+        if (h->cfg.conn_mode) {
+            ok &= cudaMalloc(&h->w_lam2, sizeof(double) * std::max<size_t>(cfg->max_scenarios, 1)) == cudaSuccess;
+            ok &= cudaMalloc(&h->w_fied, sizeof(double) * std::max<size_t>(B, 1)) == cudaSuccess;
+        }
         if (h->cfg.slack_mode) ok &= cudaMalloc(&h->w_lead, std::max<size_t>(B * (N > 1 ? N - 1 : 1), 1)) == cudaSuccess;
         if (!ok) {
             set_error("device workspace allocation failed");
@@ -464,6 +486,8 @@ int mpccbf_destroy(mpccbf_handle* h) {
         for (void* q : eptrs)
             if (q) cudaFree(q);
         if (h->w_lead) cudaFree(h->w_lead);
+        if (h->w_lam2) cudaFree(h->w_lam2);
+        if (h->w_fied) cudaFree(h->w_fied);
         void* ptrs[] = {h->d_tmpl, h->d_yw, h->d_vr, h->d_kr, h->w_states, h->w_targets, h->w_ctrl, h->w_obj,
                         h->w_status, h->w_ncurves, h->w_iters, h->o_states, h->o_ref, h->o_ctrl, h->o_all, h->o_status};
         for (void* p : ptrs)
@@ -1090,6 +1114,69 @@ int mpccbf_emul_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t a
     a.agent_begin = agent_begin;
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
+    if (h->cfg.conn_mode) {  // host stand-in for cbf_filter.cu's warp-level eigen-solve (cyclic Jacobi, same weights)
+        const int N = h->cfg.num_agents;
+        h->hc_lam2.assign(S, 0.0);
+        h->hc_fied.assign(static_cast<size_t>(S) * N, 0.0);
+        const double R2 = h->cfg.d_max * h->cfg.d_max, sigma = R2 * R2 / std::log(2.0);
+        std::vector<double> Lm(static_cast<size_t>(N) * N), Vm(static_cast<size_t>(N) * N);
+        for (int s = 0; s < S && N > 1; ++s) {
+            const double* st = states + static_cast<size_t>(s) * N * 6;
+            std::fill(Lm.begin(), Lm.end(), 0.0);
+            std::fill(Vm.begin(), Vm.end(), 0.0);
+            for (int i = 0; i < N; ++i) {
+                Vm[i * N + i] = 1.0;
+                for (int j = 0; j < N; ++j) {
+                    if (i == j) continue;
+                    const double dx = st[i * 6] - st[j * 6], dy = st[i * 6 + 1] - st[j * 6 + 1], d2 = dx * dx + dy * dy;
+                    if (d2 <= R2) {
+                        const double w = std::exp((R2 - d2) * (R2 - d2) / sigma) - 1.0;
+                        Lm[i * N + j] = -w;
+                        Lm[i * N + i] += w;
+                    }
+                }
+            }
+            for (int sweep = 0; sweep < 60; ++sweep) {
+                double off = 0.0, dg = 0.0;
+                for (int i = 0; i < N; ++i)
+                    for (int j = 0; j < N; ++j) (i == j ? dg : off) += Lm[i * N + j] * Lm[i * N + j];
+                if (!(off > 4.930380657631324e-32 * dg)) break;
+                for (int p = 0; p < N - 1; ++p)
+                    for (int q = p + 1; q < N; ++q) {
+                        const double apq = Lm[p * N + q];
+                        if (apq == 0.0) continue;
+                        const double app = Lm[p * N + p], aqq = Lm[q * N + q];
+                        const double theta = (aqq - app) / (2.0 * apq);
+                        const double t = std::copysign(1.0, theta) / (std::fabs(theta) + std::sqrt(theta * theta + 1.0));
+                        const double c = 1.0 / std::sqrt(t * t + 1.0), sn = t * c;
+                        for (int k = 0; k < N; ++k) {
+                            if (k != p && k != q) {
+                                const double akp = Lm[k * N + p], akq = Lm[k * N + q];
+                                Lm[k * N + p] = Lm[p * N + k] = c * akp - sn * akq;
+                                Lm[k * N + q] = Lm[q * N + k] = sn * akp + c * akq;
+                            }
+                            const double vkp = Vm[k * N + p], vkq = Vm[k * N + q];
+                            Vm[k * N + p] = c * vkp - sn * vkq;
+                            Vm[k * N + q] = sn * vkp + c * vkq;
+                        }
+                        Lm[p * N + p] = app - t * apq;
+                        Lm[q * N + q] = aqq + t * apq;
+                        Lm[p * N + q] = Lm[q * N + p] = 0.0;
+                    }
+            }
+            int i1 = 0, i2 = -1;
+            for (int i = 1; i < N; ++i)
+                if (Lm[i * N + i] < Lm[i1 * N + i1]) i1 = i;
+            for (int i = 0; i < N; ++i)
+                if (i != i1 && (i2 < 0 || Lm[i * N + i] < Lm[i2 * N + i2])) i2 = i;
+            h->hc_lam2[s] = Lm[i2 * N + i2];
+            double nn = 0.0;
+            for (int i = 0; i < N; ++i) nn += Vm[i * N + i2] * Vm[i * N + i2];
+            for (int i = 0; i < N; ++i) h->hc_fied[static_cast<size_t>(s) * N + i] = Vm[i * N + i2] / std::sqrt(nn);
+        }
+        a.lambda2 = h->hc_lam2.data();
+        a.fiedler = h->hc_fied.data();
+    }
     if (h->lanes > 0 || !h->dev.poly)
         emul_impc_reduced_host(h->dev, a);
     else

@@ -102,6 +102,7 @@ struct FilterArgs {
     int32_t* status;          // [S][N]      (may be NULL)
     double* lambda2;          // [S]         (may be NULL)
     double* conn_rows;        // [S][N][4] (gx, gy, 0, b), may be NULL
+    double* fiedler;          // [S][N] normalised eigenvector of lambda2, may be NULL
     int S, N, NP;             // NP: padded row length (odd)
     double dmin2, dmax, gamma, tol;
     double vmin[3], vmax[3];
@@ -220,6 +221,11 @@ __global__ void __launch_bounds__(128) cbf_filter_kernel(const FilterArgs a) {
         }
         __syncwarp();
         if (lane == 0 && a.lambda2) a.lambda2[s] = lam2;
+        if (a.fiedler && lane < N) a.fiedler[static_cast<size_t>(s) * N + lane] = fv[lane];
+        if (!a.conn_rows && !a.u) {  // only the eigenpair was wanted
+            __syncwarp();
+            continue;
+        }
 
         // ---- per agent: rows and the 3-variable QP --------------------------------------------------
         if (lane < N) {
@@ -283,12 +289,12 @@ __global__ void __launch_bounds__(128) cbf_filter_kernel(const FilterArgs a) {
 
 // Returns a cudaError_t; cudaErrorInvalidValue when N > 32 (one lane per agent).
 int launch_cbf_filter(const mpccbf_config& cfg, int S, const double* states, const double* desired_u, double* u,
-                      int32_t* status, double* lambda2, double* conn_rows, int sm_count, cudaStream_t stream) {
+                      int32_t* status, double* lambda2, double* conn_rows, int sm_count, cudaStream_t stream, double* fiedler) {
     if (S <= 0) return cudaSuccess;
     const int N = cfg.num_agents;
     if (N > 32 || N < 1) return cudaErrorInvalidValue;
     FilterArgs a;
-    a.states = states; a.desired_u = desired_u; a.u = u; a.status = status; a.lambda2 = lambda2; a.conn_rows = conn_rows;
+    a.states = states; a.desired_u = desired_u; a.u = u; a.status = status; a.lambda2 = lambda2; a.conn_rows = conn_rows; a.fiedler = fiedler;
     a.S = S; a.N = N; a.NP = N | 1;
     a.dmin2 = cfg.d_min * cfg.d_min; a.dmax = cfg.d_max;
     a.gamma = cfg.cbf_gamma > 0 ? cfg.cbf_gamma : 5.0;

@@ -79,6 +79,7 @@ int mpccbf_config_validate(const mpccbf_config* c) {
     // parseIMPCParams (parsing.hpp:121-132)
     if (c->cbf_horizon < 1) return bad("CBF horizon must be at least 1");
     if (c->impc_iter < 1) return bad("IMPC iterations must be at least 1");
+    if (c->conn_mode != 0 && c->conn_mode != 1) return bad("conn_mode must be 0 or 1");
     if (c->slack_mode && c->slack_cost <= 0)
         return bad("Slack cost must be positive when slack_mode is enabled");
     if (c->slack_mode && (c->slack_decay <= 0 || c->slack_decay > 1))

@@ -21,6 +21,8 @@ struct DevTables {
     double feas_tol;
     int32_t slack;      // slack mode: safety rows of one neighbour share a slack of weight slack_cost * slack_decay^rank
     double slack_cost, slack_decay;
+    int32_t conn_mode;  // MPC-lifted connectivity HOCBF / CLF rows (mpccbf_config::conn_mode)
+    double dmax;        // d_max: range of the proximity graph
     double Vs[2][2];    // v0 = Vs [pos;vel] + Vt target      (per axis)
     double Vt[2];
     double Kc[2][2];    // c0 = s'Kc s + target (Kt.s)        (per axis)

@@ -57,6 +57,52 @@ MPCCBF_HD void hocbf_row(double px, double py, double vx, double vy, double qx, 
     b = lf2h + lfa + gamma * psi1 * psi1 * psi1;
 }
 
+// Distance CLF row as the MPC-lifted reference inserts it (ConnectivityMPCCBFQPOperations.cpp:72-86, :152-173 with
+// initCLFCBF cbf/src/detail/ConnectivityCBF.cpp:200-243): V = (|p - p_n| - 2)^2, row  -(a.u) <= -Bc  with a = grad V,
+// Bc = Lf^2 V + 5 Lf V + 2 V (only the EGO velocity enters). Returned in the common form a.u + b >= 0, b = -Bc.
+MPCCBF_HD void clf_row_lifted(double px, double py, double vx, double vy, double qx, double qy, double& ax, double& ay, double& b) {
+    const double dx = px - qx, dy = py - qy;
+    const double d2 = dx * dx + dy * dy, dist = sqrt(d2), err = dist - 2.0;
+    const double i1 = 1.0 / dist, i2 = 1.0 / d2, i3 = i1 * i2;
+    ax = 2.0 * err * dx * i1;
+    ay = 2.0 * err * dy * i1;
+    const double hxx = 2.0 * (dx * dx * i2 + err * (i1 - dx * dx * i3));
+    const double hxy = 2.0 * (dx * dy * i2 + err * (-dx * dy * i3));
+    const double hyy = 2.0 * (dy * dy * i2 + err * (i1 - dy * dy * i3));
+    const double lfv = ax * vx + ay * vy;
+    const double lf2v = vx * (hxx * vx + hxy * vy) + vy * (hxy * vx + hyy * vy);
+    b = -(lf2v + 5.0 * lfv + 2.0 * err * err);
+}
+
+// Connectivity HOCBF row of agent `self` with its own state replaced by (px, py, vx, vy)
+// (ConnectivityMPCCBFQPOperations.cpp:45-70, :111-150; initConnCBF / compute_full_grad_h
+// cbf/src/detail/ConnectivityCBF.cpp:439-519 in closed form): h = lambda2 - 0.1, gradient and Hessian w.r.t. the
+// agent's own position with the eigenvector fv held constant, no range gating, alpha linear with gain gamma.
+MPCCBF_HD void conn_row_lifted(const double* st, int N, int self, const double* fv, double lam2, double dmax, double gamma,
+                               double px, double py, double vx, double vy, double& gx, double& gy, double& b) {
+    const double R2 = dmax * dmax, sigma = R2 * R2 / 0.6931471805599453;
+    gx = 0.0;
+    gy = 0.0;
+    double hxx = 0.0, hxy = 0.0, hyy = 0.0;
+    for (int j = 0; j < N; ++j) {
+        if (j == self) continue;
+        const double dx = px - st[j * 6], dy = py - st[j * 6 + 1];
+        const double diff = R2 - (dx * dx + dy * dy);
+        const double E = exp(diff * diff / sigma);
+        const double dvj = fv[self] - fv[j], wj = dvj * dvj;
+        const double c = -4.0 * E * diff / sigma;
+        const double cp2 = 2.0 * (4.0 * E / sigma * (2.0 * diff * diff / sigma + 1.0));
+        gx = fma(c * wj, dx, gx);
+        gy = fma(c * wj, dy, gy);
+        hxx += wj * (c + cp2 * dx * dx);
+        hxy += wj * (cp2 * dx * dy);
+        hyy += wj * (c + cp2 * dy * dy);
+    }
+    const double lfh = gx * vx + gy * vy;
+    const double lf2h = vx * (hxx * vx + hxy * vy) + vy * (hxy * vx + hyy * vy);
+    b = lf2h + gamma * lfh + gamma * (lfh + gamma * (lam2 - 0.1));
+}
+
 // one two-sided bound row: value `val`, normalisation `inv`; updates the arg-max
 MPCCBF_HD void check_two_sided(double val, double lo, double hi, double inv, double tol, int id_base, double& best,
                                int& best_id) {
@@ -229,7 +275,11 @@ struct RowsXY {
     const unsigned short* cand;  // candidate row ids: cand[i * cstride]
     int pstride, cstride;
     int ncand;            // < 0: scan all `ncbf` rows
-    int ncbf, hit, self;
+    int ncbf, hit, self;  // ncbf pairwise rows: [0, nsafe) safety HOCBF, [nsafe, ncbf) distance CLF (conn_mode, lambda2 <= 0.1)
+    int nsafe;            // (N - 1) * hit
+    int nconn;            // connectivity HOCBF rows (conn_mode, lambda2 > 0.1): row ids ncbf + k, values in conn[]
+    const double* conn;   // conn[(k * 3 + i) * cnstride] = (gx, gy, b) of horizon step k
+    int cnstride;
     double dmin2, gamma;
     int nid_fix;          // 8K
     const double (*pq)[4];  // polynomial row structure (DevTables::poly)
@@ -242,12 +292,24 @@ struct RowsXY {
     double slack_cost, slack_decay;
 
     MPCCBF_HD void cbf_row(int j, double& ax, double& ay, double& b, int& k) const {
-        const int nb = j / hit;
-        k = j - nb * hit;
+        if (j >= ncbf) {  // connectivity HOCBF row of horizon step j - ncbf (computed once per IMPC iteration)
+            k = j - ncbf;
+            ax = conn[(k * 3) * cnstride];
+            ay = conn[(k * 3 + 1) * cnstride];
+            b = conn[(k * 3 + 2) * cnstride];
+            return;
+        }
+        const bool clf = j >= nsafe;
+        const int jj = clf ? j - nsafe : j;
+        const int nb = jj / hit;
+        k = jj - nb * hit;
         const int other = nb + (nb >= self ? 1 : 0);
         const double* o = st + other * 6;
         const double* e = pred + (k * 4) * pstride;
-        hocbf_row(e[0], e[pstride], e[2 * pstride], e[3 * pstride], o[0], o[1], o[3], o[4], dmin2, gamma, ax, ay, b);
+        if (clf)
+            clf_row_lifted(e[0], e[pstride], e[2 * pstride], e[3 * pstride], o[0], o[1], ax, ay, b);
+        else
+            hocbf_row(e[0], e[pstride], e[2 * pstride], e[3 * pstride], o[0], o[1], o[3], o[4], dmin2, gamma, ax, ay, b);
     }
     // g(v) = rhs - n.v of safety row j: positive when violated
     MPCCBF_HD double cbf_g(const double (&v)[4], double ax, double ay, double b, int k) const {
@@ -318,6 +380,8 @@ struct RowsXY {
         } else {
             for (int i = 0; i < ncand; ++i) check_cbf(cand[i * cstride], v, kb, jb);
         }
+        if constexpr (!SOFT)
+            for (int k = 0; k < nconn; ++k) check_cbf(ncbf + k, v, kb, jb);
         const int kx = max(key[0], key[1]), ky = max(key[2], key[3]);
         const int kfix = max(kx, ky);
         if (kfix < 128 && jb < 0) return;  // feasible
@@ -421,6 +485,11 @@ struct AgentCtx {
     int* snapi;
     int sstride;
     unsigned char* lead;              // [N-1] group leaders of this agent (slack mode), else NULL
+    // conn_mode: algebraic connectivity and Fiedler vector of this agent's scenario, scratch for its connectivity rows
+    double lam2;
+    const double* fied;
+    double* conn;                     // [(k * 3 + i) * cnstride]
+    int cnstride;
 };
 
 // keeps the safety rows that can be violated somewhere inside the acceleration box (a row that
@@ -508,6 +577,10 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     rx.cstride = c.cstride;
     rx.ncand = 0;
     rx.ncbf = 0;
+    rx.nsafe = 0;
+    rx.nconn = 0;
+    rx.conn = c.conn;
+    rx.cnstride = c.cnstride;
     rx.hit = 1;
     rx.self = self;
     rx.dmin2 = T.dmin2;
@@ -579,11 +652,31 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                 }
                 dirty = false;
                 rx.hit = hit;
-                rx.ncbf = (N - 1) * hit;
+                rx.nsafe = (N - 1) * hit;
+                rx.ncbf = rx.nsafe;
+                rx.nconn = 0;
+                if constexpr (!SOFT) {
+                    if (T.conn_mode) {  // ConnectivityIMPCCBF.cpp:143-157 / :177-192 (commented out in the reference)
+                        if (c.lam2 > 0.1) {
+                            for (int k = 0; k < hit; ++k) {
+                                double gx2, gy2, bb;
+                                conn_row_lifted(c.st, N, self, c.fied, c.lam2, T.dmax, T.gamma, c.pred[(k * 4) * c.pstride],
+                                                c.pred[(k * 4 + 1) * c.pstride], c.pred[(k * 4 + 2) * c.pstride],
+                                                c.pred[(k * 4 + 3) * c.pstride], gx2, gy2, bb);
+                                c.conn[(k * 3) * c.cnstride] = gx2;
+                                c.conn[(k * 3 + 1) * c.cnstride] = gy2;
+                                c.conn[(k * 3 + 2) * c.cnstride] = bb;
+                            }
+                            rx.nconn = hit;
+                        } else {
+                            rx.ncbf = 2 * rx.nsafe;  // one distance-CLF row per neighbour and step after the safety rows
+                        }
+                    }
+                }
                 if constexpr (SOFT)
                     for (int nb = 0; nb < N - 1; ++nb) c.lead[nb] = 0;
                 build_candidates<SOFT>(rx, T, c.cand, c.cstride);
-                run = rx.ncand != 0;
+                run = rx.ncand != 0 || rx.nconn > 0;
             } else {
                 run = true;
             }
@@ -717,6 +810,7 @@ __host__ __device__ inline void fill_scan_tables(const DevTables& T, const doubl
 struct ThreadSmemLayout {
     int tm, yw, vr, kr, vq, omap_bytes;  // doubles (omap in bytes), CTA-shared
     int st, pred, sol, snapd, snapi_bytes, cand_bytes;   // per warp: doubles (snapi, cand in bytes)
+    int fied, conn;                  // per warp (conn_mode only): Fiedler vectors of the tile's scenarios, connectivity rows
     int nscen_max;
     size_t shared_bytes, warp_bytes;
 };
@@ -737,7 +831,9 @@ static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count) {
     L.snapi_bytes = 32 * kSnapI * 4;
     L.cand_bytes = kCandMax * 32 * 2;
     L.shared_bytes = sizeof(double) * (L.tm + L.yw + L.vr + L.kr + L.vq) + L.omap_bytes;
-    L.warp_bytes = sizeof(double) * (L.st + L.pred + L.sol + L.snapd) + L.snapi_bytes + L.cand_bytes;
+    L.fied = T.conn_mode ? L.nscen_max * T.N : 0;
+    L.conn = T.conn_mode ? std::max(T.H, 1) * 3 * 32 : 0;
+    L.warp_bytes = sizeof(double) * (L.st + L.pred + L.sol + L.snapd + L.fied + L.conn) + L.snapi_bytes + L.cand_bytes;
     return L;
 }
 
@@ -756,7 +852,9 @@ impc_thread_kernel(const __grid_constant__ DevTables T, const __grid_constant__ 
     double* wpred = wst + L.st;
     double* wsol = wpred + L.pred;
     double* wsnapd = wsol + L.sol;
-    int* wsnapi = reinterpret_cast<int*>(wsnapd + L.snapd);
+    double* wfied = wsnapd + L.snapd;
+    double* wconn = wfied + L.fied;
+    int* wsnapi = reinterpret_cast<int*>(wconn + L.conn);
     unsigned short* wcand = reinterpret_cast<unsigned short*>(reinterpret_cast<unsigned char*>(wsnapi) + L.snapi_bytes);
 
     for (int i = threadIdx.x; i < L.tm; i += blockDim.x) tm[i] = T.tmpl[i];
@@ -791,6 +889,8 @@ impc_thread_kernel(const __grid_constant__ DevTables T, const __grid_constant__ 
             double2* dst = reinterpret_cast<double2*>(wst);
             const int words = (s_hi - s_lo + 1) * N * 3;
             for (int i = lane; i < words; i += 32) dst[i] = __ldg(src + i);
+            if (L.fied)
+                for (int i = lane; i < (s_hi - s_lo + 1) * N; i += 32) wfied[i] = __ldg(a.fiedler + static_cast<size_t>(s_lo) * N + i);
         }
         __syncwarp();
         if (lane < cnt) {
@@ -811,6 +911,10 @@ impc_thread_kernel(const __grid_constant__ DevTables T, const __grid_constant__ 
             c.snapd = wsnapd + lane;
             c.snapi = wsnapi + lane;
             c.sstride = 32;
+            c.lam2 = L.fied ? __ldg(a.lambda2 + scen) : 0.0;
+            c.fied = wfied + (scen - s_lo) * N;
+            c.conn = wconn + lane;
+            c.cnstride = 32;
             c.lead = SOFT ? a.lead_ws + static_cast<size_t>(g) * (N - 1) : nullptr;
             agent_thread<SOFT>(T, a, g, self, c);
         }
@@ -844,7 +948,7 @@ impc_thread_kernel(const __grid_constant__ DevTables T, const __grid_constant__ 
 void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
     std::vector<double> pred(static_cast<size_t>(std::max(T.H, 1)) * 4), sol(kSolStride);
     std::vector<unsigned short> cand(kCandMax);
-    std::vector<double> snapd(kSnapD);
+    std::vector<double> snapd(kSnapD), connrows(static_cast<size_t>(std::max(T.H, 1)) * 3);
     std::vector<int> snapi(kSnapI);
     std::vector<double> lim(24), scn(static_cast<size_t>(4) * T.K);
     std::vector<unsigned char> lead(static_cast<size_t>(std::max(T.N, 1)));
@@ -866,6 +970,10 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
         c.snapd = snapd.data();
         c.snapi = snapi.data();
         c.sstride = 1;
+        c.lam2 = (T.conn_mode && a.lambda2) ? a.lambda2[scen] : 0.0;
+        c.fied = (T.conn_mode && a.fiedler) ? a.fiedler + static_cast<size_t>(scen) * T.N : nullptr;
+        c.conn = connrows.data();
+        c.cnstride = 1;
         c.lead = lead.data();
         if (T.slack)
             agent_thread<true>(T, a, g, self, c);
@@ -895,6 +1003,7 @@ int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cuda
     }
     if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
     if (T.slack && !a.lead_ws) return cudaErrorInvalidValue;
+    if (T.conn_mode && (!a.lambda2 || !a.fiedler)) return cudaErrorInvalidValue;
     // register budget per thread: 128 (4 CTAs of 128 threads per SM), 168 (3) or 255 (2). MPCCBF_THREAD_CTAS overrides
     // the default for experiments (profiles/r2*_occupancy.md has the measured comparison).
     static const int ctas = [] {

@@ -23,6 +23,8 @@ struct StepArgs {
     int32_t* n_curves;       // [B]   may be NULL
     double* objective;       // [B]   may be NULL
     int32_t* gi_iters;       // [B][iters] may be NULL
+    const double* lambda2 = nullptr;   // [S]    conn_mode: algebraic connectivity of every scenario (cbf_filter.cu)
+    const double* fiedler = nullptr;   // [S][N] conn_mode: its normalised eigenvector
     unsigned char* lead_ws = nullptr;  // [B][N-1] slack mode: group leaders (kernel scratch)
     int32_t num_qp;          // B = scenarios * agent_count
     int32_t agent_begin;     // first agent of each scenario handled by this launch
@@ -43,7 +45,8 @@ int launch_cbf_rows(const double* states, double* rows, int S, int N, double dmi
 int launch_rollout(const double* states, const double* ctrl, const int32_t* n_curves, double* next,
                    int B, const RolloutConst& rc, cudaStream_t stream);
 int launch_cbf_filter(const mpccbf_config& cfg, int S, const double* states, const double* desired_u, double* u,
-                      int32_t* status, double* lambda2, double* conn_rows, int sm_count, cudaStream_t stream);
+                      int32_t* status, double* lambda2, double* conn_rows, int sm_count, cudaStream_t stream,
+                      double* fiedler = nullptr);
 // Episode driver (episode.cu): one control step's worth of curve following + metric update.
 struct EpisodeArgs {
     double* states;            // [S][N][6] in: state the step was solved at; out: state after h

@@ -11,6 +11,7 @@
 
 #include "../include/mpccbf.h"  // mpccbf_config only (plain data)
 #include "bezier_model.hpp"
+#include "connectivity.hpp"
 #include "qp_solve.hpp"
 
 namespace oracle {
@@ -219,6 +220,44 @@ struct Controller {
                     cbf_row(pred_states[k].data(), nb, static_cast<int>(k), j);
             }
             ++j;
+        }
+        // The block the reference ships commented out (ConnectivityIMPCCBF.cpp:143-157 iter 0, :177-192 iter >= 1),
+        // enabled by cfg.conn_mode: lambda2 > 0.1 -> MPC-lifted connectivity HOCBF row(s)
+        // (ConnectivityMPCCBFQPOperations.cpp:45-70 / :111-150: lambda2, the eigenvector and h from the CURRENT
+        // states, the ego row of robot_states replaced by pred_states[k]), else one distance-CLF row per
+        // neighbour and step (:72-86 / :152-173, inserted as written there: -(a' U_k) x <= -Bc).
+        if (cfg.conn_mode && !slack) {
+            auto lifted = [&](const R a[3], R ub, int k) {
+                Vec<R> r(nv, R(0));
+                for (int jj = 0; jj < n; ++jj) {
+                    R sacc = 0;
+                    for (int ax = 0; ax < 3; ++ax) sacc += a[ax] * U(3 * k + ax, jj);
+                    r[jj] = R(-1.0) * sacc;
+                }
+                push(r, NEG, ub);
+            };
+            Vec<R> fv;
+            const R l2 = lambda2<R>(states, N, R(cfg.d_max), fv);
+            const int hit = (iter == 0) ? 1 : static_cast<int>(pred_states.size());
+            if (l2 > R(0.1)) {
+                std::vector<R> upd(states, states + 6 * N);
+                for (int k = 0; k < hit; ++k) {
+                    if (iter > 0)
+                        for (int cc = 0; cc < 6; ++cc) upd[6 * self + cc] = pred_states[k][cc];
+                    R a[3], bb;
+                    conn_cbf_row<R>(upd.data(), N, self, fv, l2, R(cfg.d_max), R(cfg.cbf_gamma), R(0.1), a, bb);
+                    lifted(a, bb, k);
+                }
+            } else {
+                for (int other = 0; other < N; ++other) {
+                    if (other == self) continue;
+                    for (int k = 0; k < hit; ++k) {
+                        R a[3], bc;
+                        clf_row<R>(iter == 0 ? x0 : pred_states[k].data(), states + 6 * other, a, bc);
+                        lifted(a, R(-1.0) * bc, k);
+                    }
+                }
+            }
         }
         b.n_cbf = static_cast<int>(rows.size()) - b.n_eq;
         // ConnectivityIMPCCBF.cpp:196-197 -> PiecewiseBezierMPCQPGenerator.cpp:148-164

@@ -31,6 +31,7 @@ class Config(C.Structure):
         ("feas_tol", C.c_double),
         ("admm_max_iter", C.c_int32), ("admm_check_every", C.c_int32),
         ("admm_eps", C.c_double), ("admm_rho", C.c_double), ("admm_sigma", C.c_double),
+        ("conn_mode", C.c_int32),
     ]
 
 

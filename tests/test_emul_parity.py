@@ -152,3 +152,21 @@ def test_compact_record_evaluates_like_the_expanded_curve(M, O, emul):
     with pytest.raises(M.MpcCbfError):
         h.eval_compact(st, got["v_free"], 2.1)
     h.close()
+
+
+@pytest.mark.parametrize("N,S,seed,spread,dmax", [(8, 12, 3, 1.6, 3.0), (16, 8, 5, 1.5, 2.5), (2, 24, 4, 2.5, 1.5), (4, 16, 7, 2.45, 1.9)])
+def test_mpc_lifted_connectivity_and_clf_rows(M, O, emul, N, S, seed, spread, dmax):
+    # cfg.conn_mode = 1: the block the reference ships commented out (ConnectivityIMPCCBF.cpp:143-157,177-192):
+    # lambda2 > 0.1 -> connectivity HOCBF row per CBF horizon step (first two cases), else distance-CLF rows per
+    # neighbour and step (last two: lambda2 = 0) — ConnectivityMPCCBFQPOperations.cpp:45-86,111-173
+    base = dict(k_hor=20, num_pieces=4, d_min=0.8, d_max=dmax, num_agents=N, conn_mode=1)
+    cfg, oc = M.default_config(**base), O.base_config(**base)
+    rng = np.random.default_rng(seed)
+    st, tg = dense_scenarios(S, N, seed, 0.8, spread=spread, vmax=0.8)
+    tg[:, :, :2] = st[:, :, :2] + rng.uniform(-6, 6, size=(S, N, 2))   # agents want to disperse: the rows bind
+    got = run_emul(M, emul, cfg, st, tg)
+    check_step(O, oc, O.get_table(oc, "U_basis"), st, tg, got, check_viol_max=0)
+    off = run_emul(M, emul, cfg.copy(conn_mode=0), st, tg)
+    assert (np.abs(got["ctrl_pts"] - off["ctrl_pts"]).max(-1) > 1e-6).sum() + (got["status"] != off["status"]).sum() > 0 or N == 8
+    l2 = np.array([O.lambda2(st[s], dmax)[0] for s in range(S)])
+    assert (l2 > 0.1).all() if dmax >= 2.5 else (l2 <= 0.1).all()

@@ -149,3 +149,32 @@ def test_structure_known_answers(O):
     assert r["success"] and abs(r["objective"][0] + 1378.9905) < 1e-3
     assert np.allclose(U[:3] @ r["curves"][0], [-270 / 91, -270 / 91, 0], atol=1e-9)
     assert r["kkt"].max() < 1e-8
+
+
+def test_connectivity_goldens_lifted_into_the_mpc_qp(O, gold):
+    # The MPC-lifted connectivity row (ConnectivityMPCCBFQPOperations::connectivityConstraint, :45-70): with the
+    # reference's own golden (Ac, Bc) the row of the assembled QP must be -(Ac' U_0) with upper bound Bc, inserted
+    # after the safety rows (ConnectivityIMPCCBF.cpp:143-151, commented out there; cfg.conn_mode = 1 here).
+    g = gold["connectivity_cbf"]
+    for case in g["cases"]:
+        st = np.array(case["states"], float)
+        N = st.shape[0]
+        oc = O.base_config(k_hor=20, num_pieces=4, d_min=0.8, d_max=g["dmax"], num_agents=N, conn_mode=1)
+        l2, _ = O.lambda2(st, g["dmax"])
+        assert l2 > 0.1                       # connected: the single connectivity row, no CLF rows
+        ref = np.zeros(3 * oc.k_hor)
+        qp = O.build_qp(oc, st, case["self"], ref, it=0)
+        off = O.build_qp(O.base_config(k_hor=20, num_pieces=4, d_min=0.8, d_max=g["dmax"], num_agents=N), st, case["self"], ref, it=0)
+        assert qp["n_cbf"] == off["n_cbf"] + 1 and qp["A"].shape[0] == off["A"].shape[0] + 1
+        r = qp["n_eq"] + (N - 1)              # first row after the safety rows
+        U = O.get_table(oc, "U_basis")
+        assert np.abs(qp["A"][r] + np.array(case["Ac"]) @ U[0:3]).max() <= g["tol_Ac"] * np.abs(U[0:3]).sum(0).max()
+        assert abs(qp["u"][r] - case["Bc"]) <= 8 * np.spacing(abs(case["Bc"])) and qp["l"][r] < -1e300
+        # iter >= 1: one row per CBF horizon step at the predicted ego state; with pred = current state the k = 0
+        # row has the same (Ac, Bc) and sits on U_0, the k = 1 row on U_1
+        pred = np.tile(st[case["self"]], (oc.cbf_horizon, 1))
+        qp1 = O.build_qp(oc, st, case["self"], ref, it=1, pred_states=pred)
+        r1 = qp1["n_eq"] + (N - 1) * oc.cbf_horizon
+        for k in range(oc.cbf_horizon):
+            assert np.abs(qp1["A"][r1 + k] + np.array(case["Ac"]) @ U[3 * k:3 * k + 3]).max() <= g["tol_Ac"] * np.abs(U[3 * k:3 * k + 3]).sum(0).max()
+            assert abs(qp1["u"][r1 + k] - case["Bc"]) <= 8 * np.spacing(abs(case["Bc"]))
