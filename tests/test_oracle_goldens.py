@@ -161,13 +161,23 @@ def test_connectivity_goldens_lifted_into_the_mpc_qp(O, gold):
         N = st.shape[0]
         oc = O.base_config(k_hor=20, num_pieces=4, d_min=0.8, d_max=g["dmax"], num_agents=N, conn_mode=1)
         l2, _ = O.lambda2(st, g["dmax"])
-        assert l2 > 0.1                       # connected: the single connectivity row, no CLF rows
         ref = np.zeros(3 * oc.k_hor)
         qp = O.build_qp(oc, st, case["self"], ref, it=0)
         off = O.build_qp(O.base_config(k_hor=20, num_pieces=4, d_min=0.8, d_max=g["dmax"], num_agents=N), st, case["self"], ref, it=0)
+        U = O.get_table(oc, "U_basis")
+        if l2 <= 0.1:
+            # weakly connected golden ("Misc2", lambda2 = 0.03): the controller takes the CLF branch — one row per
+            # neighbour, -(a' U_0) x <= -Bc as ConnectivityMPCCBFQPOperations::clfConstraint (:72-86) writes it
+            assert qp["n_cbf"] == off["n_cbf"] + (N - 1)
+            others = [j for j in range(N) if j != case["self"]]
+            for i, j in enumerate(others):
+                a, bc = O.clf_row(st[case["self"]], st[j])
+                r = qp["n_eq"] + (N - 1) + i
+                assert np.abs(qp["A"][r] + a @ U[0:3]).max() <= 1e-12 * np.abs(U[0:3]).sum(0).max()
+                assert abs(qp["u"][r] + bc) <= 1e-12 * max(1.0, abs(bc))
+            continue
         assert qp["n_cbf"] == off["n_cbf"] + 1 and qp["A"].shape[0] == off["A"].shape[0] + 1
         r = qp["n_eq"] + (N - 1)              # first row after the safety rows
-        U = O.get_table(oc, "U_basis")
         assert np.abs(qp["A"][r] + np.array(case["Ac"]) @ U[0:3]).max() <= g["tol_Ac"] * np.abs(U[0:3]).sum(0).max()
         assert abs(qp["u"][r] - case["Bc"]) <= 8 * np.spacing(abs(case["Bc"])) and qp["l"][r] < -1e300
         # iter >= 1: one row per CBF horizon step at the predicted ego state; with pred = current state the k = 0
