@@ -155,9 +155,9 @@ static inline int hiword_host(double x) {
 // The scan does not walk the horizon. Along the horizon the acceleration row value is affine in t_k and
 // the velocity row value quadratic, and the thresholded bounds are the same at every k, so
 // max_k |val_k - mid| is attained at an end sample or (velocity) at a sample next to the parabola's
-// vertex: "is any row violated" is decided exactly by 2 + 5 samples per axis instead of 2 K, and the
-// pivot is the candidate with the largest violation in whitened distance (any violated row is a valid
-// pivot of the dual active-set iteration; the minimiser does not depend on the choice).
+// vertex: "is any row violated" is decided exactly by 2 + 5 samples per axis instead of 2 K. Only a row family
+// (acceleration / velocity of one axis) that has a violated row is then walked over the whole horizon to pick
+// the pivot (largest violation in whitened distance).
 // scn[k] = {t_k, inv_norm_acc, inv_norm_vel, -}; kinv = (K - 1) / t_{K-1} maps a time to a sample index.
 MPCCBF_HD int key_acc(const double* scn, int k, const AxisPoly& a, double a0, double halfA) {
     const double tk = scn[4 * k], ia = scn[4 * k + 1];
@@ -179,10 +179,24 @@ MPCCBF_HD int vertex_sample(const AxisPoly& a, float kinv, int K) {
 MPCCBF_HD void scan_axis_keys(const double* scn, int K, float kinv, const AxisPoly& a, double midA, double halfA, double midV,
                               double halfV, int& keyA, int& keyV) {
     const double a0 = a.p[0] - midA, v0 = a.p[2] - midV;
-    keyA = max(keyA, max(key_acc(scn, 0, a, a0, halfA), key_acc(scn, K - 1, a, a0, halfA)));
+    int kA = max(key_acc(scn, 0, a, a0, halfA), key_acc(scn, K - 1, a, a0, halfA));
     const int kv = vertex_sample(a, kinv, K);
-    keyV = max(keyV, max(key_vel(scn, 0, a, v0, halfV), key_vel(scn, K - 1, a, v0, halfV)));
-    keyV = max(keyV, max(key_vel(scn, kv - 1, a, v0, halfV), max(key_vel(scn, kv, a, v0, halfV), key_vel(scn, kv + 1, a, v0, halfV))));
+    int kV = max(key_vel(scn, 0, a, v0, halfV), key_vel(scn, K - 1, a, v0, halfV));
+    kV = max(kV, max(key_vel(scn, kv - 1, a, v0, halfV), max(key_vel(scn, kv, a, v0, halfV), key_vel(scn, kv + 1, a, v0, halfV))));
+    // A family with a violated row: its pivot candidate is the row with the largest violation in WHITENED distance
+    // over the whole horizon (the row norms vary along the horizon, and chasing the largest raw violation from
+    // sample to sample costs about twice the active-set steps: profiles/r2_pivot_rule.md). Families without a
+    // violated row — the common case, and every final scan — stop at the 2 + 5 samples above.
+    if (kA >= 128) {
+#pragma unroll 4
+        for (int k = 1; k < K - 1; ++k) kA = max(kA, key_acc(scn, k, a, a0, halfA));
+    }
+    if (kV >= 128) {
+#pragma unroll 4
+        for (int k = 1; k < K - 1; ++k) kV = max(kV, key_vel(scn, k, a, v0, halfV));
+    }
+    keyA = max(keyA, kA);
+    keyV = max(keyV, kV);
 }
 // both x/y axes: key[ax * 2 + dsel]
 MPCCBF_HD void scan_axes_keys2(const double* scn, int K, float kinv, const AxisPoly& ax, const AxisPoly& ay, const double* lim, int (&key)[4]) {
