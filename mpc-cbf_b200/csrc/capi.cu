@@ -52,7 +52,6 @@ struct mpccbf_handle {
     // conn_mode: lambda2 [S] and Fiedler vector [S][N] of every scenario (cbf_filter.cu), refreshed before every step
     double *w_lam2 = nullptr, *w_fied = nullptr;
     std::vector<double> hc_lam2, hc_fied;  // host-only handles (tests/emul)
-    std::vector<int32_t> hc_warm;
     int64_t launches = 0, qps = 0;
 };
 
@@ -1115,13 +1114,6 @@ int mpccbf_emul_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t a
     a.agent_begin = agent_begin;
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
-    if (const char* env = std::getenv("MPCCBF_WARM_START")) {
-        if (std::atoi(env) != 0) {
-            if (h->hc_warm.size() != static_cast<size_t>(a.num_qp) * (h->cfg.impc_iter + 1) * 4)
-                h->hc_warm.assign(static_cast<size_t>(a.num_qp) * (h->cfg.impc_iter + 1) * 4, -1);
-            a.warm_ids = h->hc_warm.data();
-        }
-    }
     if (h->cfg.conn_mode) {  // host stand-in for cbf_filter.cu's warp-level eigen-solve (cyclic Jacobi, same weights)
         const int N = h->cfg.num_agents;
         h->hc_lam2.assign(S, 0.0);
