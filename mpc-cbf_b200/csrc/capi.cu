@@ -52,6 +52,21 @@ struct mpccbf_handle {
     // conn_mode: lambda2 [S] and Fiedler vector [S][N] of every scenario (cbf_filter.cu), refreshed before every step
     double *w_lam2 = nullptr, *w_fied = nullptr;
     std::vector<double> hc_lam2, hc_fied;  // host-only handles (tests/emul)
+    // Latency path for small batches (<= small_cap agents) and mpccbf_optimize_one: inputs are copied by the CPU into a
+    // pinned, device-mapped staging buffer that the kernel reads in place, outputs are stored by the kernel straight
+    // into pinned mapped memory and copied out by the CPU after the stream sync — one launch and one sync per call
+    // instead of five cudaMemcpyAsync + launch + sync.
+    size_t small_cap = 0;
+    unsigned char *pin_in = nullptr, *pin_out = nullptr;     // host addresses
+    unsigned char *pin_in_d = nullptr, *pin_out_d = nullptr;  // the same memory as the device sees it
+    struct Pending {
+        bool active = false;
+        size_t cnt = 0, n = 0, it = 0;
+        double* ctrl = nullptr;
+        int32_t* status = nullptr;
+        int32_t* n_curves = nullptr;
+        double* objective = nullptr;
+    } pending;
     int64_t launches = 0, qps = 0;
 };
 
@@ -462,6 +477,20 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
         ok &= cudaMalloc(&h->o_ctrl, sizeof(double) * n) == cudaSuccess;
         ok &= cudaMalloc(&h->o_all, sizeof(double) * n * it) == cudaSuccess;
         ok &= cudaMalloc(&h->o_status, sizeof(int32_t) * (it + 1 + it)) == cudaSuccess;
+        {
+            static const bool allow_small = [] { const char* e = std::getenv("MPCCBF_SMALL_BATCH"); return !e || std::atoi(e) != 0; }();
+            h->small_cap = allow_small ? std::min<size_t>(B, 1024) : 0;
+            const size_t in_bytes = h->small_cap * 9 * sizeof(double) + (N * 6 + 3 * K) * sizeof(double);
+            const size_t out_bytes = h->small_cap * (n * sizeof(double) + it * 4 + 4 + 8) + (n * it * sizeof(double) + (2 * it + 1) * 4) + 64;
+            if (h->small_cap > 0 &&
+                (cudaHostAlloc(reinterpret_cast<void**>(&h->pin_in), in_bytes, cudaHostAllocMapped) != cudaSuccess ||
+                 cudaHostAlloc(reinterpret_cast<void**>(&h->pin_out), out_bytes, cudaHostAllocMapped) != cudaSuccess ||
+                 cudaHostGetDevicePointer(reinterpret_cast<void**>(&h->pin_in_d), h->pin_in, 0) != cudaSuccess ||
+                 cudaHostGetDevicePointer(reinterpret_cast<void**>(&h->pin_out_d), h->pin_out, 0) != cudaSuccess)) {
+                (void)cudaGetLastError();
+                h->small_cap = 0;  // no mapped pinned memory: the staged-copy path serves every size
+            }
+        }
         if (h->cfg.conn_mode) {
             ok &= cudaMalloc(&h->w_lam2, sizeof(double) * std::max<size_t>(cfg->max_scenarios, 1)) == cudaSuccess;
             ok &= cudaMalloc(&h->w_fied, sizeof(double) * std::max<size_t>(B, 1)) == cudaSuccess;
@@ -487,6 +516,8 @@ int mpccbf_destroy(mpccbf_handle* h) {
             if (q) cudaFree(q);
         if (h->w_lead) cudaFree(h->w_lead);
         if (h->w_lam2) cudaFree(h->w_lam2);
+        if (h->pin_in) cudaFreeHost(h->pin_in);
+        if (h->pin_out) cudaFreeHost(h->pin_out);
         if (h->w_fied) cudaFree(h->w_fied);
         void* ptrs[] = {h->d_tmpl, h->d_yw, h->d_vr, h->d_kr, h->w_states, h->w_targets, h->w_ctrl, h->w_obj,
                         h->w_status, h->w_ncurves, h->w_iters, h->o_states, h->o_ref, h->o_ctrl, h->o_all, h->o_status};
@@ -578,6 +609,18 @@ int mpccbf_synchronize(mpccbf_handle* h) {
     CUDA_TRY(cudaSetDevice(h->device));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream2));
+    if (h->pending.active) {  // small-batch latency path: results sit in the pinned staging buffer
+        const mpccbf_handle::Pending& p = h->pending;
+        const unsigned char* o = h->pin_out;
+        std::memcpy(p.ctrl, o, sizeof(double) * p.cnt * p.n);
+        o += sizeof(double) * p.cnt * p.n;
+        if (p.objective) std::memcpy(p.objective, o, sizeof(double) * p.cnt);
+        o += sizeof(double) * p.cnt;
+        std::memcpy(p.status, o, sizeof(int32_t) * p.cnt * p.it);
+        o += sizeof(int32_t) * p.cnt * p.it;
+        if (p.n_curves) std::memcpy(p.n_curves, o, sizeof(int32_t) * p.cnt);
+        h->pending.active = false;
+    }
     return MPCCBF_OK;
 }
 
@@ -716,6 +759,29 @@ static int step_host_enqueue(mpccbf_handle* h, int32_t S, const double* states, 
     // kernel stores them straight into it — coalesced posted writes over PCIe that overlap the solve —
     // instead of writing HBM and copying afterwards. The small per-agent outputs (status, n_curves,
     // objective) are single 4/8-byte stores and stay on the copy path. MPCCBF_ZEROCOPY=0 disables it.
+    if (static_cast<size_t>(S) * N <= h->small_cap) {
+        if (h->pending.active) {  // an earlier small batch has not been collected yet: finish it first
+            rc = mpccbf_synchronize(h);
+            if (rc != MPCCBF_OK) return rc;
+        }
+        const size_t cnt = static_cast<size_t>(S) * N;
+        double* in = reinterpret_cast<double*>(h->pin_in);
+        std::memcpy(in, states, sizeof(double) * cnt * 6);
+        std::memcpy(in + cnt * 6, targets, sizeof(double) * cnt * 3);
+        const double* in_d = reinterpret_cast<const double*>(h->pin_in_d);
+        unsigned char* o = h->pin_out_d;
+        double* ctrl_d = reinterpret_cast<double*>(o);
+        double* obj_d = reinterpret_cast<double*>(o + sizeof(double) * cnt * n);
+        int32_t* status_d = reinterpret_cast<int32_t*>(o + sizeof(double) * cnt * (n + 1));
+        int32_t* nc_d = status_d + cnt * it;
+        rc = run_step(h, S, 0, h->cfg.num_agents, in_d, in_d + cnt * 6, 0, compact ? nullptr : ctrl_d, nullptr, compact ? ctrl_d : nullptr,
+                      status_d, nc_d, obj_d, h->w_iters, h->stream);
+        if (rc != MPCCBF_OK) return rc;
+        h->pending.active = true;
+        h->pending.cnt = cnt; h->pending.n = n; h->pending.it = it;
+        h->pending.ctrl = ctrl_pts; h->pending.status = status; h->pending.n_curves = n_curves; h->pending.objective = objective;
+        return MPCCBF_OK;
+    }
     double* ctrl_dev = nullptr;
     const double *states_dev = nullptr, *targets_dev = nullptr;  // pinned inputs are read in place as well
     {
@@ -776,6 +842,29 @@ int mpccbf_optimize_one(mpccbf_handle* h, const double* states, int32_t self_idx
     }
     CUDA_TRY(cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
+    if (h->small_cap > 0) {
+        // latency path: pinned mapped staging, one launch + one sync (see mpccbf_handle::pin_in)
+        if (h->pending.active) {
+            rc = mpccbf_synchronize(h);
+            if (rc != MPCCBF_OK) return rc;
+        }
+        double* in = reinterpret_cast<double*>(h->pin_in + h->small_cap * 9 * sizeof(double));
+        std::memcpy(in, states, sizeof(double) * N * 6);
+        std::memcpy(in + N * 6, ref, sizeof(double) * 3 * K);
+        const double* in_d = reinterpret_cast<const double*>(h->pin_in_d + h->small_cap * 9 * sizeof(double));
+        const size_t off = ((h->small_cap * (static_cast<size_t>(n) * sizeof(double) + it * 4 + 4 + 8) + 63) / 64) * 64;
+        double* all_d = reinterpret_cast<double*>(h->pin_out_d + off);
+        int32_t* st_d = reinterpret_cast<int32_t*>(h->pin_out_d + off + sizeof(double) * n * it);
+        const double* all_h = reinterpret_cast<const double*>(h->pin_out + off);
+        const int32_t* st_h = reinterpret_cast<const int32_t*>(h->pin_out + off + sizeof(double) * n * it);
+        rc = run_step(h, 1, self_idx, 1, in_d, in_d + N * 6, 1, nullptr, all_d, nullptr, st_d, st_d + it, nullptr, st_d + it + 1, st);
+        if (rc != MPCCBF_OK) return rc;
+        CUDA_TRY(cudaStreamSynchronize(st));
+        for (int i = 0; i < it; ++i) status[i] = st_h[i];
+        *n_curves = st_h[it];
+        if (st_h[it] > 0) std::memcpy(ctrl_pts, all_h, sizeof(double) * n * st_h[it]);
+        return MPCCBF_OK;
+    }
     CUDA_TRY(cudaMemcpyAsync(h->o_states, states, sizeof(double) * N * 6, cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(h->o_ref, ref, sizeof(double) * 3 * K, cudaMemcpyHostToDevice, st));
     int32_t* d_status = h->o_status;
