@@ -31,7 +31,7 @@ for K in (10, 20, 40):
 
 def run_bench(S, N, K, steps, warmup):
     cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--scenarios", str(S), "--agents", str(N), "--k-hor", str(K),
-           "--steps", str(steps), "--warmup", str(warmup), "--no-cpu-baseline", "--snapshots", "4"]
+           "--steps", str(steps), "--warmup", str(warmup), "--no-cpu-baseline", "--no-extras", "--snapshots", "4"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     if r.returncode != 0:
         return {"error": (r.stderr or r.stdout)[-400:]}
@@ -127,9 +127,9 @@ def main():
                 f.write(f"| {d['label']} | error: {d['error'][-120:]} | | | | | | |\n")
                 continue
             c, r = d["config"], d["roofline"]
-            f.write(f"| {d['label']} | {c['qps_per_step_per_gpu'] // (2 * c['agents'])} x {c['agents']}, {c['k_hor']} | {d['value']:.4g} | "
+            f.write(f"| {d['label']} | {c['scenarios_total']} x {c['agents']}, {c['k_hor']} | {d['value']:.4g} | "
                     f"{d['e2e']['value']:.4g} | {d['p50_step_ms']:.4f} | {d['p99_step_ms']:.4f} | "
-                    f"{r['fp64']['mean_active_set_iterations_per_qp']:.2f} | {r['fp64']['frac']:.3f} |\n")
+                    f"{r['mean_active_set_iterations_per_qp']:.2f} | {r['frac']:.3f} |\n")
     rows = filter_and_episode(a.out)
     for r in rows:
         print(json.dumps(r))

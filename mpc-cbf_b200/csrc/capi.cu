@@ -599,6 +599,10 @@ int mpccbf_copy_iteration_counts(mpccbf_handle* h, int32_t* out_host, int64_t co
         return MPCCBF_ERR_INVALID;
     }
     CUDA_TRY(cudaSetDevice(h->device));
+    // the handle's own streams are non-blocking (not ordered against the legacy stream cudaMemcpy uses): finish
+    // them first. A step enqueued on a CALLER's stream is the caller's to synchronise (documented in mpccbf.h).
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream2));
     CUDA_TRY(cudaMemcpy(out_host, h->w_iters, sizeof(int32_t) * count, cudaMemcpyDeviceToHost));
     return MPCCBF_OK;
 }
