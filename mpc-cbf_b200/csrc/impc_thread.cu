@@ -155,9 +155,9 @@ static inline int hiword_host(double x) {
 // The scan does not walk the horizon. Along the horizon the acceleration row value is affine in t_k and
 // the velocity row value quadratic, and the thresholded bounds are the same at every k, so
 // max_k |val_k - mid| is attained at an end sample or (velocity) at a sample next to the parabola's
-// vertex: "is any row violated" is decided exactly by 2 + 5 samples per axis instead of 2 K. Only a row family
-// (acceleration / velocity of one axis) that has a violated row is then walked over the whole horizon to pick
-// the pivot (largest violation in whitened distance).
+// vertex: "is any row violated" is decided exactly by 2 + 5 samples per axis instead of 2 K. Only a velocity
+// family that has a violated row is then searched along the horizon for the pivot (largest violation in whitened
+// distance).
 // scn[k] = {t_k, inv_norm_acc, inv_norm_vel, -}; kinv = (K - 1) / t_{K-1} maps a time to a sample index.
 MPCCBF_HD int key_acc(const double* scn, int k, const AxisPoly& a, double a0, double halfA) {
     const double tk = scn[4 * k], ia = scn[4 * k + 1];
@@ -183,17 +183,21 @@ MPCCBF_HD void scan_axis_keys(const double* scn, int K, float kinv, const AxisPo
     const int kv = vertex_sample(a, kinv, K);
     int kV = max(key_vel(scn, 0, a, v0, halfV), key_vel(scn, K - 1, a, v0, halfV));
     kV = max(kV, max(key_vel(scn, kv - 1, a, v0, halfV), max(key_vel(scn, kv, a, v0, halfV), key_vel(scn, kv + 1, a, v0, halfV))));
-    // A family with a violated row: its pivot candidate is the row with the largest violation in WHITENED distance
-    // over the whole horizon (the row norms vary along the horizon, and chasing the largest raw violation from
-    // sample to sample costs about twice the active-set steps: profiles/r2_pivot_rule.md). Families without a
-    // violated row — the common case, and every final scan — stop at the 2 + 5 samples above.
-    if (kA >= 128) {
-#pragma unroll 4
-        for (int k = 1; k < K - 1; ++k) kA = max(kA, key_acc(scn, k, a, a0, halfA));
-    }
+    // A velocity family with a violated row: its pivot candidate is the row with the largest violation in WHITENED
+    // distance over the whole horizon — the row norms grow along the horizon, and chasing the largest raw violation
+    // (which sits at the vertex) costs 74 % more active-set steps (profiles/r2_warm_start_and_pivot_rule.md). The score is
+    // smooth in k, so a stride-s walk refined around its best sample finds the same pivots as the full walk
+    // (measured: identical step counts). The acceleration family is affine: its end samples suffice (measured likewise).
+    // Families without a violated row — the common case, and every final scan — stop at the 2 + 5 samples above.
     if (kV >= 128) {
-#pragma unroll 4
-        for (int k = 1; k < K - 1; ++k) kV = max(kV, key_vel(scn, k, a, v0, halfV));
+        const int s = K >= 30 ? 5 : 3;
+#pragma unroll 2
+        for (int k = s; k < K - 1; k += s) kV = max(kV, key_vel(scn, k, a, v0, halfV));
+        const int kb = kV & 127;
+        for (int dk = 1; dk < s; ++dk) {
+            if (kb - dk >= 0) kV = max(kV, key_vel(scn, kb - dk, a, v0, halfV));
+            if (kb + dk < K) kV = max(kV, key_vel(scn, kb + dk, a, v0, halfV));
+        }
     }
     keyA = max(keyA, kA);
     keyV = max(keyV, kV);
@@ -509,20 +513,35 @@ struct AgentCtx {
 // keeps the safety rows that can be violated somewhere inside the acceleration box (a row that
 // holds on the whole box holds at every point the bound rows admit, so dropping it is exact)
 template <bool SOFT>
-MPCCBF_HD void build_candidates(RowsXY<SOFT>& rx, const DevTables& T, unsigned short* cand, int cstride) {
+MPCCBF_HD void build_candidates(RowsXY<SOFT>& rx, const DevTables& T, unsigned short* cand, int cstride, unsigned long long& k0mask,
+                                 bool& k0valid) {
+    // The predicted ego state at t_0 = 0 is the current state (the curve is pinned there by the initial-state rows), so
+    // the k = 0 safety row of neighbour nb is the same row in every IMPC iteration: its candidate test is done once
+    // (iteration 0) and remembered in a bit mask while the neighbours fit one.
     int nc = 0;
     const bool wide = rx.ncbf > 65535;
+    const bool fill = rx.hit == 1 && rx.nnb <= 64;
+    const bool reuse = k0valid && !fill;
+    if (fill) k0mask = 0ull;
     for (int j = 0; j < rx.ncbf && !wide; ++j) {
-        double ax, ay, b;
-        int k;
-        rx.cbf_row(j, ax, ay, b, k);
-        if (!(fabs(b) < 1e20)) continue;  // CPLEX: |bound| >= 1e20 is "no bound"
-        const double mn = fmin(ax * T.lim_lo[0][0], ax * T.lim_hi[0][0]) + fmin(ay * T.lim_lo[0][1], ay * T.lim_hi[0][1]);
-        if (!(mn + b > 1e-7 * (1.0 + fabs(ax) + fabs(ay)))) {
+        bool keep;
+        if (reuse && j < rx.nsafe && (j % rx.hit) == 0) {
+            keep = (k0mask >> (j / rx.hit)) & 1ull;
+        } else {
+            double ax, ay, b;
+            int k;
+            rx.cbf_row(j, ax, ay, b, k);
+            if (!(fabs(b) < 1e20)) continue;  // CPLEX: |bound| >= 1e20 is "no bound"
+            const double mn = fmin(ax * T.lim_lo[0][0], ax * T.lim_hi[0][0]) + fmin(ay * T.lim_lo[0][1], ay * T.lim_hi[0][1]);
+            keep = !(mn + b > 1e-7 * (1.0 + fabs(ax) + fabs(ay)));
+            if (fill && keep && j < rx.nsafe) k0mask |= 1ull << j;
+        }
+        if (keep) {
             if (nc < kCandMax) cand[nc * cstride] = static_cast<unsigned short>(j);
             ++nc;
         }
     }
+    if (fill) k0valid = true;
     rx.ncand = (wide || nc > kCandMax) ? -1 : nc;
 }
 
@@ -625,6 +644,8 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     // safety rows into the active set, the stage-A factorisation is restored from `snap`.
     enum { kStageA = 0, kIter = 2 };
     int n_ok = 0;
+    unsigned long long k0mask = 0ull;  // candidate flags of the k = 0 safety rows (same rows in every IMPC iteration)
+    bool k0valid = false;
     bool dirty = false;  // gx has safety rows in its active set (not reusable as stage A)
     double pen_last = 0.0;  // slack mode: sum_j w_j s_j of the last successful iterate
     const size_t sbase = static_cast<size_t>(g) * T.iters;
@@ -689,7 +710,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                 }
                 if constexpr (SOFT)
                     for (int nb = 0; nb < N - 1; ++nb) c.lead[nb] = 0;
-                build_candidates<SOFT>(rx, T, c.cand, c.cstride);
+                build_candidates<SOFT>(rx, T, c.cand, c.cstride, k0mask, k0valid);
                 run = rx.ncand != 0 || rx.nconn > 0;
             } else {
                 run = true;
