@@ -47,9 +47,12 @@ extern "C" {
 
 /* Which solver the controller path uses. */
 #define MPCCBF_SOLVER_AUTO 0     /* reduced when the structure allows, else dense           */
-#define MPCCBF_SOLVER_REDUCED 1  /* fused null-space active-set kernel (C^3 cubic pieces),  */
-                                 /* with or without slack_mode                              */
-#define MPCCBF_SOLVER_DENSE 2    /* the configuration does not reduce: only the S-qp seam   */
+#define MPCCBF_SOLVER_REDUCED 1  /* fused null-space active-set kernels: cubic C^3 pieces   */
+                                 /* (2 free dof per axis; slack_mode, conn_mode, compact    */
+                                 /* results) or any configuration with 1..8 free dof per    */
+                                 /* axis (general kernel)                                   */
+#define MPCCBF_SOLVER_DENSE 2    /* the equality rows are rank-deficient or leave more than */
+                                 /* 8 free dof per axis: only the S-qp seam                 */
                                  /* (mpccbf_solve_qp_dense, ADMM/OSQP kernel) is available  */
 
 /* Configuration: union of the reference's parameter structs

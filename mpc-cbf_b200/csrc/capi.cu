@@ -26,6 +26,10 @@ struct mpccbf_handle {
     mpccbf_config cfg;
     HostTables tab;
     DevTables dev;
+    GenTables gen;            // general reduced kernel (r != 2 free dof per axis), see impc_general.cu
+    bool general = false;
+    std::vector<double> g_gt, g_vs, g_vt, g_vr, g_kr, g_yw;
+    double *dg_gt = nullptr, *dg_vs = nullptr, *dg_vt = nullptr, *dg_vr = nullptr, *dg_kr = nullptr, *dg_yw = nullptr;
     RolloutConst rc;
     bool has_device = false;
     int device = -1;
@@ -150,6 +154,78 @@ int build_device_tables(mpccbf_handle* h) {
             bernstein_deriv(t.c, h->cfg.piece_max_param, local, 1, row);
             for (int j = 0; j < t.c; ++j) rc.b1[j] = static_cast<double>(row[j]);
         }
+    }
+    if (t.reducible && t.r1 >= 1 && t.r1 <= kGenMaxR && t.r1 != 2) {
+        // ---- general reduced kernel: same whitened null-space coordinates, r free dof per axis ------------------
+        GenTables& G = h->gen;
+        std::memset(&G, 0, sizeof(G));
+        const int K = t.K, r = t.r1;
+        G.K = K; G.r = r; G.m1 = t.m1; G.n = t.n; G.c = t.c; G.p = t.p;
+        G.N = h->cfg.num_agents; G.H = h->cfg.cbf_horizon; G.iters = h->cfg.impc_iter;
+        G.max_gi = 50 * (6 * r + 12 * K + (d.N - 1) * d.H) + 100;
+        std::memcpy(G.lim_lo, d.lim_lo, sizeof(G.lim_lo));
+        std::memcpy(G.lim_hi, d.lim_hi, sizeof(G.lim_hi));
+        G.dmin2 = d.dmin2; G.gamma = d.gamma; G.feas_tol = d.feas_tol;
+        for (int i = 0; i < 2; ++i) {
+            xreal sk = 0.0L;
+            for (int k = 0; k < K; ++k) sk += t.Kr(i, k);
+            G.Kt[i] = static_cast<double>(sk);
+            for (int j = 0; j < 2; ++j) G.Kc[i][j] = static_cast<double>(t.Kc(i, j));
+        }
+        h->g_gt.assign(static_cast<size_t>(3) * K * (r + 2), 0.0);
+        for (int dd = 0; dd < 3; ++dd) {
+            xreal nmax = 0.0L;
+            std::vector<xreal> nrm(K, 0.0L);
+            for (int k = 0; k < K; ++k) {
+                for (int j = 0; j < r; ++j) nrm[k] += t.Ct[dd](k, j) * t.Ct[dd](k, j);
+                nrm[k] = std::sqrt(nrm[k]);
+                nmax = std::max(nmax, nrm[k]);
+            }
+            for (int k = 0; k < K; ++k) {
+                double* e = &h->g_gt[(static_cast<size_t>(dd) * K + k) * (r + 2)];
+                const bool constant_row = !(nrm[k] > 1e-12L * std::max(nmax, 1e-300L));  // pinned by the equality rows
+                for (int j = 0; j < r; ++j) e[j] = constant_row ? 0.0 : static_cast<double>(t.Ct[dd](k, j));
+                e[r] = static_cast<double>(t.Ot[dd](k, 0));
+                e[r + 1] = static_cast<double>(t.Ot[dd](k, 1));
+            }
+        }
+        h->g_vs.assign(static_cast<size_t>(r) * 2, 0.0);
+        h->g_vt.assign(r, 0.0);
+        h->g_vr.assign(static_cast<size_t>(r) * K, 0.0);
+        h->g_kr.assign(static_cast<size_t>(2) * K, 0.0);
+        h->g_yw.assign(static_cast<size_t>(t.m1) * (2 + r), 0.0);
+        for (int j = 0; j < r; ++j) {
+            xreal sv = 0.0L;
+            for (int k = 0; k < K; ++k) {
+                h->g_vr[static_cast<size_t>(j) * K + k] = static_cast<double>(t.Vr(j, k));
+                sv += t.Vr(j, k);
+            }
+            h->g_vt[j] = static_cast<double>(sv);
+            h->g_vs[2 * j] = static_cast<double>(t.Vs(j, 0));
+            h->g_vs[2 * j + 1] = static_cast<double>(t.Vs(j, 1));
+        }
+        for (int i = 0; i < 2; ++i)
+            for (int k = 0; k < K; ++k) h->g_kr[static_cast<size_t>(i) * K + k] = static_cast<double>(t.Kr(i, k));
+        for (int i = 0; i < t.m1; ++i) {
+            h->g_yw[static_cast<size_t>(i) * (2 + r)] = static_cast<double>(t.Y1(i, 0));
+            h->g_yw[static_cast<size_t>(i) * (2 + r) + 1] = static_cast<double>(t.Y1(i, 1));
+            for (int j = 0; j < r; ++j) h->g_yw[static_cast<size_t>(i) * (2 + r) + 2 + j] = static_cast<double>(t.W1(i, j));
+        }
+        if (h->has_device) {
+            int rc;
+            if ((rc = upload(h->g_gt, &h->dg_gt)) != MPCCBF_OK) return rc;
+            if ((rc = upload(h->g_vs, &h->dg_vs)) != MPCCBF_OK) return rc;
+            if ((rc = upload(h->g_vt, &h->dg_vt)) != MPCCBF_OK) return rc;
+            if ((rc = upload(h->g_vr, &h->dg_vr)) != MPCCBF_OK) return rc;
+            if ((rc = upload(h->g_kr, &h->dg_kr)) != MPCCBF_OK) return rc;
+            if ((rc = upload(h->g_yw, &h->dg_yw)) != MPCCBF_OK) return rc;
+            G.gt = h->dg_gt; G.vs = h->dg_vs; G.vt = h->dg_vt; G.vr = h->dg_vr; G.kr = h->dg_kr; G.yw = h->dg_yw;
+        } else {
+            G.gt = h->g_gt.data(); G.vs = h->g_vs.data(); G.vt = h->g_vt.data(); G.vr = h->g_vr.data();
+            G.kr = h->g_kr.data(); G.yw = h->g_yw.data();
+        }
+        h->general = true;
+        return MPCCBF_OK;
     }
     if (!(t.reducible && t.r1 == 2)) return MPCCBF_OK;
     const int K = t.K;
@@ -348,6 +424,16 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
     a.lead_ws = h->w_lead;
+    if (h->general) {
+        if (v_out) {
+            set_error("the compact result form needs cubic pieces with C^3 continuity (2 free dof per axis)");
+            return MPCCBF_ERR_UNSUPPORTED;
+        }
+        CUDA_TRY(launch_impc_general(h->gen, a, h->sm_count, stream));
+        h->launches += 1;
+        h->qps += static_cast<int64_t>(a.num_qp) * h->cfg.impc_iter;
+        return MPCCBF_OK;
+    }
     if (h->cfg.conn_mode) {  // one warp per scenario: Laplacian, Jacobi eigen-solve, second smallest eigenpair
         CUDA_TRY(launch_cbf_filter(h->cfg, S, states, nullptr, nullptr, nullptr, h->w_lam2, nullptr, h->sm_count, stream, h->w_fied));
         a.lambda2 = h->w_lam2;
@@ -401,7 +487,7 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
         delete h;
         return MPCCBF_ERR_INVALID;
     }
-    const bool can_reduce = h->tab.reducible && h->tab.r1 == 2 && h->cfg.num_agents >= 1;
+    const bool can_reduce = h->tab.reducible && h->tab.r1 >= 1 && h->tab.r1 <= kGenMaxR && h->cfg.cbf_horizon <= 8 && h->cfg.num_agents >= 1;
     if (cfg->solver == MPCCBF_SOLVER_REDUCED && !can_reduce) {
         set_error("MPCCBF_SOLVER_REDUCED requested but the configuration does not reduce to the 6-dof form");
         delete h;
@@ -447,6 +533,12 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
     if (rc != MPCCBF_OK) {
         mpccbf_destroy(h);
         return rc;
+    }
+    if (h->general && (h->cfg.slack_mode || h->cfg.conn_mode)) {
+        set_error("slack_mode / conn_mode need cubic pieces with C^3 continuity (the fused thread-per-agent kernel); this "
+                  "configuration is served by the general reduced kernel");
+        mpccbf_destroy(h);
+        return MPCCBF_ERR_UNSUPPORTED;
     }
     if (h->cfg.conn_mode && (h->cfg.slack_mode || h->cfg.num_agents > 32 || h->solver != MPCCBF_SOLVER_REDUCED || !h->dev.poly)) {
         set_error("conn_mode needs slack_mode = 0 (the reference indexes the slack of the connectivity row by self_idx, out of "
@@ -519,6 +611,9 @@ int mpccbf_destroy(mpccbf_handle* h) {
         if (h->pin_in) cudaFreeHost(h->pin_in);
         if (h->pin_out) cudaFreeHost(h->pin_out);
         if (h->w_fied) cudaFree(h->w_fied);
+        void* gptrs[] = {h->dg_gt, h->dg_vs, h->dg_vt, h->dg_vr, h->dg_kr, h->dg_yw};
+        for (void* q : gptrs)
+            if (q) cudaFree(q);
         void* ptrs[] = {h->d_tmpl, h->d_yw, h->d_vr, h->d_kr, h->w_states, h->w_targets, h->w_ctrl, h->w_obj,
                         h->w_status, h->w_ncurves, h->w_iters, h->o_states, h->o_ref, h->o_ctrl, h->o_all, h->o_status};
         for (void* p : ptrs)
@@ -679,8 +774,8 @@ int mpccbf_expand_ctrl_pts(const mpccbf_handle* h, int64_t count, const double* 
         set_error("mpccbf_expand_ctrl_pts: invalid argument");
         return MPCCBF_ERR_INVALID;
     }
-    if (h->solver != MPCCBF_SOLVER_REDUCED) {
-        set_error("mpccbf_expand_ctrl_pts: the configuration has no reduced form");
+    if (h->solver != MPCCBF_SOLVER_REDUCED || h->general) {
+        set_error("mpccbf_expand_ctrl_pts: the compact form needs cubic pieces with C^3 continuity");
         return MPCCBF_ERR_UNSUPPORTED;
     }
     const int n = h->tab.n, c = h->tab.c, m1 = h->tab.m1;
@@ -711,8 +806,8 @@ int mpccbf_eval_compact(const mpccbf_handle* h, int64_t count, const double* sta
         set_error("mpccbf_eval_compact: invalid argument");
         return MPCCBF_ERR_INVALID;
     }
-    if (h->solver != MPCCBF_SOLVER_REDUCED || h->tab.c > 8) {
-        set_error("mpccbf_eval_compact: the configuration has no reduced form");
+    if (h->solver != MPCCBF_SOLVER_REDUCED || h->general || h->tab.c > 8) {
+        set_error("mpccbf_eval_compact: the compact form needs cubic pieces with C^3 continuity");
         return MPCCBF_ERR_UNSUPPORTED;
     }
     const int c = h->tab.c, p = h->tab.p;
@@ -1207,6 +1302,10 @@ int mpccbf_emul_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t a
     a.agent_begin = agent_begin;
     a.agent_count = agent_count;
     a.ref_mode = ref_mode;
+    if (h->general) {
+        emul_impc_general_host(h->gen, a);
+        return MPCCBF_OK;
+    }
     if (h->cfg.conn_mode) {  // host stand-in for cbf_filter.cu's warp-level eigen-solve (cyclic Jacobi, same weights)
         const int N = h->cfg.num_agents;
         h->hc_lam2.assign(S, 0.0);

@@ -38,6 +38,22 @@ struct RolloutConst {
     double b0[8], b1[8];
 };
 
+// Tables of the general reduced kernel (impc_general.cu): r free dof per axis, any continuity degree / control-point count.
+constexpr int kGenMaxR = 8;
+struct GenTables {
+    int32_t K, r, m1, n, c, p, N, H, iters, max_gi;
+    double lim_lo[2][3], lim_hi[2][3];  // [0] acceleration rows, [1] velocity rows
+    double dmin2, gamma, feas_tol;
+    double Kc[2][2], Kt[2];
+    const double* gt;   // [3][K][r + 2]  d = 0 pos, 1 vel, 2 acc: {Ct (r), Ot (2)}; rows independent of v have Ct = 0 exactly
+    const double* vs;   // [r][2]
+    const double* vt;   // [r]     row sums of vr (constant reference)
+    const double* vr;   // [r][K]
+    const double* kr;   // [2][K]
+    const double* yw;   // [m1][2 + r]  {Y1 (2), W1 (r)}
+};
+int launch_impc_general(const GenTables& T, const StepArgs& a, int sm_count, cudaStream_t stream);
+
 int launch_impc_reduced(const DevTables& T, const StepArgs& a, int width, int sm_count, cudaStream_t stream);
 int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cudaStream_t stream);
 int launch_cbf_rows(const double* states, double* rows, int S, int N, double dmin2, double gamma,
@@ -99,6 +115,7 @@ void set_error(const std::string& msg);
 #ifdef MPCCBF_HOST_EMUL
 void emul_impc_reduced_host(const DevTables& T, const StepArgs& a);
 void emul_impc_thread_host(const DevTables& T, const StepArgs& a);
+void emul_impc_general_host(const GenTables& T, const StepArgs& a);
 #endif
 
 }  // namespace mpccbf

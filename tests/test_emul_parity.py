@@ -22,7 +22,7 @@ def emul(M):
     return L
 
 
-def run_emul(M, L, cfg, states, targets):
+def run_emul(M, L, cfg, states, targets, compact=True):
     cfg = cfg.copy(device=-1)
     h = M.Handle(cfg, library=L)
     assert h.solver == M.SOLVER_REDUCED
@@ -34,12 +34,13 @@ def run_emul(M, L, cfg, states, targets):
     st, tg = np.ascontiguousarray(states), np.ascontiguousarray(targets)
     rc = L.mpccbf_emul_step(h._h, S, 0, N, 0, st.ctypes.data, tg.ctypes.data, out["ctrl_pts"].ctypes.data, None,
                             out["status"].ctypes.data, out["n_curves"].ctypes.data, out["objective"].ctypes.data,
-                            iters.ctypes.data, out["v_free"].ctypes.data)
+                            iters.ctypes.data, out["v_free"].ctypes.data if compact else None)
     assert rc == 0
     out["iters"] = iters
     # compact result form: the host-side expansion reproduces the kernel's control points bit for bit, and
     # evaluating the curve from the compact record equals evaluating the expanded curve
-    assert np.array_equal(h.expand_ctrl_pts(st, out["v_free"], out["n_curves"]).reshape(S, N, -1), out["ctrl_pts"])
+    if compact:
+        assert np.array_equal(h.expand_ctrl_pts(st, out["v_free"], out["n_curves"]).reshape(S, N, -1), out["ctrl_pts"])
     h.close()
     return out
 
@@ -170,3 +171,23 @@ def test_mpc_lifted_connectivity_and_clf_rows(M, O, emul, N, S, seed, spread, dm
     assert (np.abs(got["ctrl_pts"] - off["ctrl_pts"]).max(-1) > 1e-6).sum() + (got["status"] != off["status"]).sum() > 0 or N == 8
     l2 = np.array([O.lambda2(st[s], dmax)[0] for s in range(S)])
     assert (l2 > 0.1).all() if dmax >= 2.5 else (l2 <= 0.1).all()
+
+
+@pytest.mark.parametrize("extra,N,S", [
+    (dict(continuity_degree=2), 8, 8),                                        # C^2 cubics: 5 free dof per axis
+    (dict(continuity_degree=1), 6, 6),                                        # C^1 cubics: 8
+    (dict(num_ctrl_pts=5, continuity_degree=3), 6, 6),                        # quartic pieces
+    (dict(num_ctrl_pts=5, continuity_degree=2, k_hor=16, num_pieces=3), 4, 8),
+])
+def test_general_configurations(M, O, emul, extra, N, S):
+    # bezier_continuity_upto_degree / num_control_points other than the shipped cubic C^3 (parsing.hpp:20-28): the
+    # general reduced kernel (impc_general.cu, r free dof per axis) against the oracle's full-space QP
+    base = dict(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N)
+    base.update(extra)
+    cfg, oc = M.default_config(**base), O.base_config(**base)
+    st, tg = dense_scenarios(S, N, 5, 0.8, spread=1.3, vmax=1.0)
+    st[0, 0, 3] = 2.5
+    got = run_emul(M, emul, cfg, st, tg, compact=False)
+    check_step(O, oc, O.get_table(oc, "U_basis"), st, tg, got, check_viol_max=4)
+    assert list(got["status"][0, 0]) == [M.STATUS_INFEASIBLE, M.STATUS_SKIPPED]
+    assert (got["status"] == M.STATUS_OPTIMAL).any()

@@ -183,3 +183,37 @@ def test_compact_result_form_is_the_same_answer(M, O, S, N):
     a = int(np.argmax(full["n_curves"][S - 1] > 0))
     assert np.abs(pos[S - 1, a] - O.eval_curve(oc, full["ctrl_pts"][S - 1, a], cfg.h, 0)).max() <= 1e-12
     h.close()
+
+
+@pytest.mark.parametrize("extra,N,S", [
+    (dict(continuity_degree=2), 8, 64),
+    (dict(continuity_degree=1), 6, 32),
+    (dict(num_ctrl_pts=5, continuity_degree=3), 6, 32),
+    (dict(num_ctrl_pts=5, continuity_degree=2, k_hor=16, num_pieces=3), 4, 64),
+])
+def test_general_configurations_on_the_device(M, O, extra, N, S):
+    # non-default continuity degree / control-point count: impc_general_kernel (r free dof per axis) through the same
+    # controller entries, closed loop of 3 steps against the oracle; the compact form is refused for them
+    base = dict(k_hor=20, num_pieces=4, d_min=0.8, num_agents=N)
+    base.update(extra)
+    cfg, oc = M.default_config(max_scenarios=S, **base), O.base_config(**base)
+    h = M.Handle(cfg)
+    assert h.solver == M.SOLVER_REDUCED
+    st, tg = dense_scenarios(S, N, 5, 0.8, spread=1.3, vmax=1.0)
+    st[0, 0, 3] = 2.5
+    U = O.get_table(oc, "U_basis")
+    for _ in range(3):
+        got = h.step_batch_host(st, tg)
+        check_step(O, oc, U, st, tg, got, check_viol_max=2)
+        for s in range(S):
+            for a in range(N):
+                if got["n_curves"][s, a] > 0:
+                    st[s, a, :3] = O.eval_curve(oc, got["ctrl_pts"][s, a], cfg.h, 0)
+                    st[s, a, 3:] = O.eval_curve(oc, got["ctrl_pts"][s, a], cfg.h, 1)
+        st[0, 0, 3] = 2.5
+    r = h.optimize_one(st[1], 0, np.tile(tg[1, 0], cfg.k_hor))
+    ro = O.optimize(oc, st[1], 0, np.tile(tg[1, 0], cfg.k_hor))
+    assert list(r["status"]) == list(ro["status"]) and np.abs(r["curves"] - ro["curves"]).max() <= 1e-5
+    with pytest.raises(M.MpcCbfError):
+        h.step_batch_host_compact(st, tg)
+    h.close()
