@@ -98,6 +98,10 @@ struct GenState {
 // Dual active-set iteration (Goldfarb-Idnani, least-distance form) with run-time dimension D <= GD.
 __host__ __device__ int gen_solve(GenState& g, const GenRows& rows, int nrows, int max_iter, int& n_iter) {
     const int D = rows.D;
+    // divergence guard (see gi_solver.h): an iterate 1e7 times farther out than v0 proves infeasibility
+    double vmax2 = 1.0;
+    for (int i = 0; i < D; ++i) vmax2 = fma(g.v[i], g.v[i], vmax2);
+    vmax2 *= 1e14;
     const double tol = rows.T->feas_tol;
     double np[GD], z[GD], d1[GD], rr[GD], w[GD];
     double Q[GD][GD], R[GD][GD];
@@ -188,6 +192,11 @@ __host__ __device__ int gen_solve(GenState& g, const GenRows& rows, int nrows, i
                 for (int i = 0; i < D; ++i) g.v[i] = fma(t, z[i], g.v[i]);
             for (int j = 0; j < g.q; ++j) g.u[j] = fma(-t, rr[j], g.u[j]);
             up_mult += t;
+            {
+                double vv = 0.0;
+                for (int i = 0; i < D; ++i) vv = fma(g.v[i], g.v[i], vv);
+                if (!(vv <= vmax2)) return MPCCBF_STATUS_INFEASIBLE;
+            }
             if (!z_zero && t2 <= t1) {
                 g.u[g.q] = up_mult;
                 g.id[g.q] = best_id;

@@ -27,8 +27,11 @@
 
 namespace mpccbf {
 
-#ifndef MPCCBF_THREAD_MIN_CTAS
-#define MPCCBF_THREAD_MIN_CTAS 4
+#ifndef MPCCBF_THREAD_CORE
+#define MPCCBF_THREAD_CORE 0
+#endif
+#ifndef MPCCBF_THREAD_CFG
+#define MPCCBF_THREAD_CFG 0
 #endif
 constexpr int kCandMax = 32;   // candidate safety rows kept per agent (more: scan all rows)
 constexpr int kSolStride = 7;  // per-agent result record: v[6] (whitened free dof of the last successful iterate), n_ok
@@ -281,7 +284,7 @@ MPCCBF_HD double slack_weight(const double* st, int self, int j, int J, double c
 // SOFT (slack mode): the safety rows of neighbour nb form a group with one slack (gi_solver.h). Row ids
 // are then nid_fix + nb * (hit + 1) + kk with kk < hit the row of horizon step kk and kk == hit the
 // piece "none"; lead[nb] = 0 while the group's slack is zero, else 1 + the horizon step of its leader.
-template <bool SOFT>
+template <bool SOFT, bool CONN>
 struct RowsXY {
     const double* tm;
     int K;
@@ -310,16 +313,23 @@ struct RowsXY {
     double slack_cost, slack_decay;
 
     MPCCBF_HD void cbf_row(int j, double& ax, double& ay, double& b, int& k) const {
-        if (j >= ncbf) {  // connectivity HOCBF row of horizon step j - ncbf (computed once per IMPC iteration)
-            k = j - ncbf;
-            ax = conn[(k * 3) * cnstride];
-            ay = conn[(k * 3 + 1) * cnstride];
-            b = conn[(k * 3 + 2) * cnstride];
-            return;
+        if constexpr (CONN) {
+            if (j >= ncbf) {  // connectivity HOCBF row of horizon step j - ncbf (computed once per IMPC iteration)
+                k = j - ncbf;
+                ax = conn[(k * 3) * cnstride];
+                ay = conn[(k * 3 + 1) * cnstride];
+                b = conn[(k * 3 + 2) * cnstride];
+                return;
+            }
         }
-        const bool clf = j >= nsafe;
-        const int jj = clf ? j - nsafe : j;
-        const int nb = jj / hit;
+        bool clf = false;
+        int jj = j;
+        if constexpr (CONN) {
+            clf = j >= nsafe;
+            if (clf) jj = j - nsafe;
+        }
+        // hit is 1 (IMPC iteration 0) or cbf_horizon (2 in every shipped config): no general integer division
+        const int nb = (hit == 1) ? jj : ((hit == 2) ? (jj >> 1) : jj / hit);
         k = jj - nb * hit;
         const int other = nb + (nb >= self ? 1 : 0);
         const double* o = st + other * 6;
@@ -356,7 +366,7 @@ struct RowsXY {
             return;
         }
         // a violated soft row that does not depend on v is taken up by its slack: large finite score
-        const int nb = j / hit;
+        const int nb = (hit == 1) ? j : ((hit == 2) ? (j >> 1) : j / hit);
         const int ld = lead[nb];
         double viol, thr = tol * fmax(1.0, fabs(b)), score;
         int id = nb * (hit + 1) + k;
@@ -398,7 +408,7 @@ struct RowsXY {
         } else {
             for (int i = 0; i < ncand; ++i) check_cbf(cand[i * cstride], v, kb, jb);
         }
-        if constexpr (!SOFT)
+        if constexpr (CONN)
             for (int k = 0; k < nconn; ++k) check_cbf(ncbf + k, v, kb, jb);
         const int kx = max(key[0], key[1]), ky = max(key[2], key[3]);
         const int kfix = max(kx, ky);
@@ -512,8 +522,8 @@ struct AgentCtx {
 
 // keeps the safety rows that can be violated somewhere inside the acceleration box (a row that
 // holds on the whole box holds at every point the bound rows admit, so dropping it is exact)
-template <bool SOFT>
-MPCCBF_HD void build_candidates(RowsXY<SOFT>& rx, const DevTables& T, unsigned short* cand, int cstride, unsigned long long& k0mask,
+template <bool SOFT, bool CONN>
+MPCCBF_HD void build_candidates(RowsXY<SOFT, CONN>& rx, const DevTables& T, unsigned short* cand, int cstride, unsigned long long& k0mask,
                                  bool& k0valid) {
     // The predicted ego state at t_0 = 0 is the current state (the curve is pinned there by the initial-state rows), so
     // the k = 0 safety row of neighbour nb is the same row in every IMPC iteration: its candidate test is done once
@@ -525,8 +535,9 @@ MPCCBF_HD void build_candidates(RowsXY<SOFT>& rx, const DevTables& T, unsigned s
     if (fill) k0mask = 0ull;
     for (int j = 0; j < rx.ncbf && !wide; ++j) {
         bool keep;
-        if (reuse && j < rx.nsafe && (j % rx.hit) == 0) {
-            keep = (k0mask >> (j / rx.hit)) & 1ull;
+        const int jnb = (rx.hit == 2) ? (j >> 1) : j / rx.hit;
+        if (reuse && j < rx.nsafe && j == jnb * rx.hit) {
+            keep = (k0mask >> jnb) & 1ull;
         } else {
             double ax, ay, b;
             int k;
@@ -559,8 +570,8 @@ template <bool WANT_C0>
 MPCCBF_HD void unconstrained_minimiser(const DevTables& T, const StepArgs& a, int g, const double (&s)[3][2], const AgentCtx& c,
                                        double (&v0)[6], double& c0);
 
-// Everything optimize() does for agent-QP g (one thread).
-template <bool SOFT>
+// Everything optimize() does for agent-QP g (one thread). CORE selects the active-set core (gi_solver.h).
+template <bool SOFT, bool CONN, int CORE>
 __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int g, int self, const AgentCtx& c) {
     const int K = T.K, N = T.N, H = T.H;
     double s[3][2];
@@ -577,8 +588,8 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     const float kinv = static_cast<float>((K - 1) / c.scn[4 * (K - 1)]);
     int total_iter = 0;
     // ---- yaw: 2-dof projection, shared by every IMPC iteration --------------------------------
-    GIState<2> gy;
-    gi_init<2>(gy, v0 + 4);
+    typename GICore<2, CORE>::State gy;
+    GICore<2, CORE>::init(gy, v0 + 4);
     int base_status;
     {
         RowsAxis ry;
@@ -591,10 +602,11 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         ry.scn = c.scn;
         ry.kinv = kinv;
         ry.lim = c.lim + 16;
-        base_status = gi_run<2>(gy, ry, T.max_gi, total_iter);
+        GISoft<2> gsy;
+        base_status = GICore<2, CORE>::template run<false>(gy, gsy, ry, T.max_gi, total_iter, gi_vmax2<2>(v0 + 4));
     }
     // ---- x/y stage A: bound rows only ---------------------------------------------------------
-    RowsXY<SOFT> rx;
+    RowsXY<SOFT, CONN> rx;
     rx.tm = c.tm;
     rx.K = K;
 #pragma unroll
@@ -627,14 +639,15 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     rx.nnb = N - 1;
     rx.slack_cost = T.slack_cost;
     rx.slack_decay = T.slack_decay;
-    GIState<4> gx;
+    typename GICore<4, CORE>::State gx;
     GISoft<4> gs;
+    const double vmax2 = gi_vmax2<4>(v0);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         gs.grp[i] = -1;
         gs.cap[i] = HUGE_VAL;
     }
-    gi_init<4>(gx, v0);
+    GICore<4, CORE>::init(gx, v0);
     // stage-A solution: iterate, multipliers and ids of its active bound rows (the factorisation is
     // rebuilt from the ids when a later IMPC iteration has to start from it again)
 
@@ -684,13 +697,14 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                         if constexpr (SOFT) gs.grp[i] = -1;
                     }
                     gx.q = c.snapi[4 * c.sstride];
+                    GICore<4, CORE>::refactor(gx, rx);
                 }
                 dirty = false;
                 rx.hit = hit;
                 rx.nsafe = (N - 1) * hit;
                 rx.ncbf = rx.nsafe;
                 rx.nconn = 0;
-                if constexpr (!SOFT) {
+                if constexpr (CONN) {
                     if (T.conn_mode) {  // ConnectivityIMPCCBF.cpp:143-157 / :177-192 (commented out in the reference)
                         if (c.lam2 > 0.1) {
                             for (int k = 0; k < hit; ++k) {
@@ -710,14 +724,14 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                 }
                 if constexpr (SOFT)
                     for (int nb = 0; nb < N - 1; ++nb) c.lead[nb] = 0;
-                build_candidates<SOFT>(rx, T, c.cand, c.cstride, k0mask, k0valid);
+                build_candidates<SOFT, CONN>(rx, T, c.cand, c.cstride, k0mask, k0valid);
                 run = rx.ncand != 0 || rx.nconn > 0;
             } else {
                 run = true;
             }
         }
         int n2 = 0;
-        if (run) stat = gi_run<4, SOFT>(gx, gs, rx, T.max_gi, n2);
+        if (run) stat = GICore<4, CORE>::template run<SOFT>(gx, gs, rx, T.max_gi, n2, vmax2);
         it_iter += n2;
         if (mode == kStageA) {
             base_status = stat;
@@ -872,9 +886,32 @@ static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count) {
     return L;
 }
 
-template <bool SOFT, int MIN_CTAS>
-__global__ void __launch_bounds__(128, MIN_CTAS)
+// Launch shapes (threads per CTA, CTAs per SM the register budget is set for). All keep >= 14 warps per SM, which is what
+// one wave of the 4096 x 16 workload needs on 148 SMs:  0: 128 x 4 (128 registers / thread)   1: 448 x 1 (146; the constant
+// tables are staged once per SM)   2: 224 x 2 (146)
+template <int CFG> struct ThreadCfg;
+template <> struct ThreadCfg<0> { static constexpr int kThreads = 128, kCtas = 4; };
+template <> struct ThreadCfg<1> { static constexpr int kThreads = 448, kCtas = 1; };
+template <> struct ThreadCfg<2> { static constexpr int kThreads = 224, kCtas = 2; };
+
+// ptxas derives 128 registers from __launch_bounds__(448, 1) and (224, 2) alike (it budgets for 512 threads), although
+// 14 warps x 32 x 144 registers fit the 64 K register file: shapes 1 and 2 state their budget with __maxnreg__ instead.
+template <bool SOFT, bool CONN, int CORE>
+__device__ __forceinline__ void thread_kernel_body(const DevTables& T, const StepArgs& a, const ThreadSmemLayout& L);
+
+template <bool SOFT, bool CONN, int CORE, int CFG>
+__global__ void __launch_bounds__(128, 4)
 impc_thread_kernel(const __grid_constant__ DevTables T, const __grid_constant__ StepArgs a, const __grid_constant__ ThreadSmemLayout L) {
+    thread_kernel_body<SOFT, CONN, CORE>(T, a, L);
+}
+template <bool SOFT, bool CONN, int CORE, int CFG>
+__global__ void __maxnreg__(144)
+impc_thread_kernel_r144(const __grid_constant__ DevTables T, const __grid_constant__ StepArgs a, const __grid_constant__ ThreadSmemLayout L) {
+    thread_kernel_body<SOFT, CONN, CORE>(T, a, L);
+}
+
+template <bool SOFT, bool CONN, int CORE>
+__device__ __forceinline__ void thread_kernel_body(const DevTables& T, const StepArgs& a, const ThreadSmemLayout& L) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* tm = reinterpret_cast<double*>(smem_raw);
     double* yw = tm + L.tm;
@@ -951,23 +988,27 @@ impc_thread_kernel(const __grid_constant__ DevTables T, const __grid_constant__ 
             c.conn = wconn + lane;
             c.cnstride = 32;
             c.lead = SOFT ? a.lead_ws + static_cast<size_t>(g) * (N - 1) : nullptr;
-            agent_thread<SOFT>(T, a, g, self, c);
+            agent_thread<SOFT, CONN, CORE>(T, a, g, self, c);
         }
         __syncwarp();
         if (a.v_out) {  // compact result: the 6 whitened free dof per agent, coalesced
             double* vo = a.v_out + static_cast<size_t>(g0) * 6;
             for (int idx = lane; idx < cnt * 6; idx += 32) {
-                const int ag = idx / 6, i = idx - ag * 6;
+                const int ag = __float2int_rz((idx + 0.5f) * (1.0f / 6.0f)), i = idx - ag * 6;
                 vo[idx] = wsol[ag * kSolStride + i];   // zeros when the agent has no curve
             }
         }
         if (a.ctrl_pts) {   // control points of the last successful iterate: coalesced stores, whole warp
             double* out = a.ctrl_pts + static_cast<size_t>(g0) * n;
             const int total = cnt * n;
+            const float inv_n = 1.0f / static_cast<float>(n);
+            // the tile's agents in order: scenario / agent-in-scenario advance without a division per element
             for (int idx = lane; idx < total; idx += 32) {
-                const int ag = idx / n, i = idx - ag * n;
+                const int ag = __float2int_rz((idx + 0.5f) * inv_n), i = idx - ag * n;   // exact: idx < 32 n
                 const double* rec = wsol + ag * kSolStride;
-                const int gg = g0 + ag, sc = gg / a.agent_count;
+                const int gg = g0 + ag;
+                int sc = s_lo;                                   // a tile spans at most nscen_max scenarios
+                while ((sc + 1) * a.agent_count <= gg) ++sc;
                 const double* sta = wst + ((sc - s_lo) * N + a.agent_begin + (gg - sc * a.agent_count)) * 6;
                 const unsigned m = omap[i];
                 const int ax = m & 3;
@@ -1010,10 +1051,14 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
         c.conn = connrows.data();
         c.cnstride = 1;
         c.lead = lead.data();
-        if (T.slack)
-            agent_thread<true>(T, a, g, self, c);
-        else
-            agent_thread<false>(T, a, g, self, c);
+        static const int core = [] { const char* e = std::getenv("MPCCBF_THREAD_CORE"); return e ? std::atoi(e) : MPCCBF_THREAD_CORE; }();
+        if (T.slack) {
+            if (core == 1) agent_thread<true, false, 1>(T, a, g, self, c); else agent_thread<true, false, 0>(T, a, g, self, c);
+        } else if (T.conn_mode) {
+            if (core == 1) agent_thread<false, true, 1>(T, a, g, self, c); else agent_thread<false, true, 0>(T, a, g, self, c);
+        } else {
+            if (core == 1) agent_thread<false, false, 1>(T, a, g, self, c); else agent_thread<false, false, 0>(T, a, g, self, c);
+        }
         if (a.v_out)
             for (int i = 0; i < 6; ++i) a.v_out[static_cast<size_t>(g) * 6 + i] = sol[i];
         double* out = a.ctrl_pts + static_cast<size_t>(g) * T.n;
@@ -1027,35 +1072,57 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
 #endif
 
 // Launches the thread-per-agent kernel. Returns a cudaError_t.
+typedef void (*ThreadKernel)(const DevTables, const StepArgs, const ThreadSmemLayout);
+
+template <int CORE, int CFG>
+static ThreadKernel pick_kernel(const DevTables& T) {
+    if (CFG == 0) {
+        if (T.slack) return impc_thread_kernel<true, false, CORE, 0>;
+        if (T.conn_mode) return impc_thread_kernel<false, true, CORE, 0>;
+        return impc_thread_kernel<false, false, CORE, 0>;
+    }
+    if (T.slack) return impc_thread_kernel_r144<true, false, CORE, 0>;
+    if (T.conn_mode) return impc_thread_kernel_r144<false, true, CORE, 0>;
+    return impc_thread_kernel_r144<false, false, CORE, 0>;
+}
+
 int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cudaStream_t stream) {
     if (a.num_qp <= 0) return cudaSuccess;
+    if (T.slack && !a.lead_ws) return cudaErrorInvalidValue;
+    if (T.conn_mode && (!a.lambda2 || !a.fiedler)) return cudaErrorInvalidValue;
+    // Active-set core and launch shape: measured defaults (profiles/r2*_variants.md); MPCCBF_THREAD_CORE = 0 / 1 and
+    // MPCCBF_THREAD_CFG = 0 / 1 / 2 override them for experiments.
+    static const int core = [] { const char* e = std::getenv("MPCCBF_THREAD_CORE"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CORE; return v == 1 ? 1 : 0; }();
+    static const int cfgi = [] { const char* e = std::getenv("MPCCBF_THREAD_CFG"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CFG; return (v == 1 || v == 2) ? v : 0; }();
+    ThreadKernel kern;
+    int threads;
+    if (cfgi == 1) {
+        kern = core ? pick_kernel<1, 1>(T) : pick_kernel<0, 1>(T);
+        threads = ThreadCfg<1>::kThreads;
+    } else if (cfgi == 2) {
+        kern = core ? pick_kernel<1, 2>(T) : pick_kernel<0, 2>(T);
+        threads = ThreadCfg<2>::kThreads;
+    } else {
+        kern = core ? pick_kernel<1, 0>(T) : pick_kernel<0, 0>(T);
+        threads = ThreadCfg<0>::kThreads;
+    }
     const ThreadSmemLayout L = thread_layout(T, a.agent_count);
-    int threads = 128;
+    const int ntiles = (a.num_qp + 31) / 32;
+    // small batches: no more warps per CTA than there are tiles per SM (keeps the grid spread over the SMs)
+    const int want = std::max(1, (ntiles + sm_count - 1) / std::max(1, sm_count));
+    while (threads > 32 && threads / 32 > want && (threads / 32) % 2 == 0 && threads > 128) threads /= 2;
     size_t smem = L.shared_bytes + L.warp_bytes * (threads / 32);
-    while (smem > 100 * 1024 && threads > 32) {
-        threads /= 2;
+    while (smem > 227 * 1024 && threads > 32) {
+        threads = std::max(32, (threads / 64) * 32);
         smem = L.shared_bytes + L.warp_bytes * (threads / 32);
     }
     if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
-    if (T.slack && !a.lead_ws) return cudaErrorInvalidValue;
-    if (T.conn_mode && (!a.lambda2 || !a.fiedler)) return cudaErrorInvalidValue;
-    // register budget per thread: 128 (4 CTAs of 128 threads per SM), 168 (3) or 255 (2). MPCCBF_THREAD_CTAS overrides
-    // the default for experiments (profiles/r2*_occupancy.md has the measured comparison).
-    static const int ctas = [] {
-        const char* e = std::getenv("MPCCBF_THREAD_CTAS");
-        const int v = e ? std::atoi(e) : MPCCBF_THREAD_MIN_CTAS;
-        return (v == 2 || v == 3) ? v : 4;
-    }();
-    auto kern = T.slack ? impc_thread_kernel<true, 4> : impc_thread_kernel<false, 4>;
-    if (ctas == 3) kern = T.slack ? impc_thread_kernel<true, 3> : impc_thread_kernel<false, 3>;
-    if (ctas == 2) kern = T.slack ? impc_thread_kernel<true, 2> : impc_thread_kernel<false, 2>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return e;
     int per_sm = 1;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) per_sm = 1;
-    const int ntiles = (a.num_qp + 31) / 32;
     const int need = (ntiles + threads / 32 - 1) / (threads / 32);
     int grid = sm_count * per_sm;  // persistent: a multiple of the SM count
     if (need < grid) grid = need;
