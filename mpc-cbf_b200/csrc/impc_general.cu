@@ -76,7 +76,7 @@ struct GenRows {
         const double psi1 = lfh + T->gamma * h * h * h;
         const double ax = 2.0 * dx, ay = 2.0 * dy, b = lf2h + lfa + T->gamma * psi1 * psi1 * psi1;
         bound_abs = fabs(b);
-        if (!(bound_abs < 1e20)) return false;
+        if (!(b < 1e20)) return false;  // one-sided: an upper bound >= 1e20 is "no bound"
         const double* t = T->gt + (static_cast<size_t>(2) * K + k) * (r + 2);  // acceleration at t_k
         for (int i = 0; i < r; ++i) {
             np[i] = ax * t[i];

@@ -141,7 +141,7 @@ __host__ __device__ int solve_projection(const QPData& qp, const double (&v0)[R]
                 const double accy = t[0] * v[2] + t[1] * v[3] + (t[2] * qp.s[1][0] + t[3] * qp.s[1][1]);
                 const double* c = qp.cbf + 4 * j;
                 const double viol = -(c[0] * accx + c[1] * accy + c[2]);
-                if (viol > qp.tol * fmax(1.0, fabs(c[2])) && fabs(c[2]) < 1e20) {
+                if (viol > qp.tol * fmax(1.0, fabs(c[2])) && c[2] < 1e20) {
                     const double score = viol * c[3];
                     if (score > best) {
                         best = score;

@@ -352,7 +352,7 @@ struct RowsXY {
         cbf_row(j, ax, ay, b, k);
         const double* t = tm + (2 * K + k) * kTmplStride;
         const double g = cbf_g(v, ax, ay, b, k);
-        if (!(fabs(b) < 1e20)) return;
+        if (!(b < 1e20)) return;
         if constexpr (!SOFT) {
             if (g > tol * fmax(1.0, fabs(b))) {
                 const double an2 = fma(ax, ax, ay * ay);
@@ -542,7 +542,7 @@ MPCCBF_HD void build_candidates(RowsXY<SOFT, CONN>& rx, const DevTables& T, unsi
             double ax, ay, b;
             int k;
             rx.cbf_row(j, ax, ay, b, k);
-            if (!(fabs(b) < 1e20)) continue;  // CPLEX: |bound| >= 1e20 is "no bound"
+            if (!(b < 1e20)) continue;  // CPLEX: an upper bound >= 1e20 is "no bound" (b <= -1e20 still binds)
             const double mn = fmin(ax * T.lim_lo[0][0], ax * T.lim_hi[0][0]) + fmin(ay * T.lim_lo[0][1], ay * T.lim_hi[0][1]);
             keep = !(mn + b > 1e-7 * (1.0 + fabs(ax) + fabs(ay)));
             if (fill && keep && j < rx.nsafe) k0mask |= 1ull << j;

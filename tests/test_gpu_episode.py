@@ -233,6 +233,9 @@ def test_episode_box_collision_shape_of_the_reference_configs(M):
     st, tg = swarm(S, N, seed=9)
     st[:, :, :2] *= 0.45
     tg[:, :, :2] *= 0.45
+    st[0, :, :2] *= 3.0 / 0.45       # scenario 0: spread out and already at its goals, so it succeeds for every box
+    st[0, :, 3:] = 0.0
+    tg[0] = st[0, :, :3]
     seen = set()
     for half in ((0.2, 0.2), (0.45, 0.3), (0.7, 0.7)):
         h, res = run(M, cfg, st, tg, steps, 1.0, 0.2, box_half=half)
