@@ -210,6 +210,23 @@ int mpccbf_solve_qp_dense(mpccbf_handle* h, int32_t batch, int32_t n, int32_t m,
                           const double* lb, const double* ub, double* x, double* objective,
                           int32_t* status, int32_t* iters);
 
+/* Allocation-free variant of mpccbf_solve_qp_dense. It has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it). Same kernel, same results; what differs:
+ *   - P, q, A, l, u, x, objective, status, iters are DEVICE pointers on the CURRENT device (all required except
+ *     A, l, u when m == 0); variable bounds are passed as rows of A; no handle: cfg (may be NULL = defaults)
+ *     only supplies admm_max_iter / admm_check_every / admm_eps / admm_rho / admm_sigma;
+ *   - asynchronous on cuda_stream (a cudaStream_t, NULL = default stream): one memset + one kernel launch, no
+ *     cudaMalloc / cudaFree / host synchronisation;
+ *   - the kernel's scratch (scaled P~ [batch][n*n]; scaled A [batch][m][n|1] when it does not fit in shared
+ *     memory) is a file-scope device array of MPCCBF_NOALLOC_SCRATCH_BYTES that every GPU which loads the library
+ *     holds until exit. A call needing more returns MPCCBF_ERR_UNSUPPORTED (message in mpccbf_last_error()).
+ *     Every call on a device shares the array: calls that overlap on the GPU (different streams, or threads) race. */
+#define MPCCBF_NOALLOC_SCRATCH_BYTES (8u << 20)
+int mpccbf_solve_qp_dense_noalloc(const mpccbf_config* cfg, int32_t batch, int32_t n, int32_t m, const double* P,
+                                  const double* q, const double* A, const double* l, const double* u, double* x,
+                                  double* objective, int32_t* status, int32_t* iters, void* cuda_stream);
+
 /* Sub-kernel K1: pairwise safety HOCBF rows for every ordered (ego, neighbour) pair at the
  * CURRENT states (iter-0 rows, ConnectivityIMPCCBF.cpp:135-141; closed form of
  * ConnectivityCBF.cpp:152-198). rows [S][N][N-1][4] = (ax, ay, az=0, b) meaning a.u + b >= 0,

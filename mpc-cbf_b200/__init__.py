@@ -39,7 +39,7 @@ EXPORTED_SYMBOLS = [
     "mpccbf_follow_reset", "mpccbf_follow_step", "mpccbf_set_kernel_variant", "mpccbf_auto_kernel_variant",
     "mpccbf_multi_create", "mpccbf_multi_destroy", "mpccbf_multi_num_devices", "mpccbf_multi_comm_ranks",
     "mpccbf_multi_handle", "mpccbf_multi_step_batch_host", "mpccbf_multi_step_batch_host_compact",
-    "mpccbf_multi_run_sharded",
+    "mpccbf_multi_run_sharded", "mpccbf_solve_qp_dense_noalloc",
 ]
 
 
@@ -167,6 +167,7 @@ def lib(path=None):
     L.mpccbf_step_agents.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
     L.mpccbf_optimize_one.argtypes = [vp, vp, i32, vp, vp, vp, vp]
     L.mpccbf_solve_qp_dense.argtypes = [vp, i32, i32, i32] + [vp] * 11
+    L.mpccbf_solve_qp_dense_noalloc.argtypes = [C.POINTER(Config), i32, i32, i32] + [vp] * 10
     L.mpccbf_cbf_rows.argtypes = [vp, i32, vp, vp, vp]
     L.mpccbf_rollout.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     L.mpccbf_cbf_filter_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
@@ -227,6 +228,22 @@ def _ptr(t):
     if isinstance(t, np.ndarray):
         return t.ctypes.data
     return t.data_ptr()
+
+
+NOALLOC_SCRATCH_BYTES = 8 << 20   # MPCCBF_NOALLOC_SCRATCH_BYTES (include/mpccbf.h)
+
+
+def solve_qp_dense_noalloc(cfg, P, q, A, l, u, x, objective, status, iters, stream=None, library=None):
+    """mpccbf_solve_qp_dense_noalloc: DEVICE tensors in and out (current device), asynchronous on `stream`,
+    scratch in the library's fixed device array. Raises MpcCbfError (e.g. scratch limit exceeded)."""
+    L = library if library is not None else lib()
+    batch, n = q.shape
+    m = l.shape[1] if l is not None else 0
+    rc = L.mpccbf_solve_qp_dense_noalloc(C.byref(cfg) if cfg is not None else None, batch, n, m, _ptr(P), _ptr(q),
+                                         _ptr(A) if m else None, _ptr(l) if m else None, _ptr(u) if m else None,
+                                         _ptr(x), _ptr(objective), _ptr(status), _ptr(iters), stream)
+    if rc != OK:
+        raise MpcCbfError(rc, L.mpccbf_last_error().decode())
 
 
 class Handle:

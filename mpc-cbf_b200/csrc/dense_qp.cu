@@ -917,3 +917,85 @@ done:
 }
 
 }  // namespace mpccbf
+
+// ---- allocation-free entry (mpccbf_solve_qp_dense_noalloc) ----------------------------------------------------------
+// For callers that may not call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it): the
+// kernel's per-QP scratch (scaled P~, and scaled A when it does not fit in shared memory) lives in a file-scope device
+// array of fixed size instead of an allocation. Every GPU that loads the library holds the array until exit; every call
+// shares it, so calls that overlap on the GPU race. The kernel writes each QP's scratch before it reads it; the used
+// part is cleared first all the same, so a result cannot depend on what the previous call left behind.
+namespace {
+
+constexpr size_t kNoAllocDoubles = MPCCBF_NOALLOC_SCRATCH_BYTES / sizeof(double);
+static __device__ __align__(256) double g_noalloc_scratch[kNoAllocDoubles];
+
+constexpr int kNoAllocMaxDevices = 64;
+double* g_noalloc_ptr[kNoAllocMaxDevices];  // device address of g_noalloc_scratch per device (the name is a host stand-in)
+
+// Once per device, with that device current: the device address of the array.
+int noalloc_scratch(double** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kNoAllocMaxDevices) {
+        mpccbf::set_error(std::string("mpccbf_solve_qp_dense_noalloc: cudaGetDevice: ") +
+                          (e != cudaSuccess ? cudaGetErrorString(e) : "device ordinal out of range"));
+        return MPCCBF_ERR_CUDA;
+    }
+    double* p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        void* sym = nullptr;
+        e = cudaGetSymbolAddress(&sym, g_noalloc_scratch);
+        if (e != cudaSuccess || !sym) {
+            mpccbf::set_error(std::string("mpccbf_solve_qp_dense_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+            return MPCCBF_ERR_CUDA;
+        }
+        p = static_cast<double*>(sym);
+        __atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);  // every thread computes the same value
+    }
+    *out = p;
+    return MPCCBF_OK;
+}
+
+}  // namespace
+
+extern "C" int mpccbf_solve_qp_dense_noalloc(const mpccbf_config* cfg, int32_t batch, int32_t n, int32_t m, const double* P,
+                                             const double* q, const double* A, const double* l, const double* u, double* x,
+                                             double* objective, int32_t* status, int32_t* iters, void* cuda_stream) {
+    using namespace mpccbf;
+    if (batch < 0 || n < 1 || m < 0 || !P || !q || (m > 0 && (!A || !l || !u)) || !x || !objective || !status || !iters) {
+        set_error("mpccbf_solve_qp_dense_noalloc: invalid argument");
+        return MPCCBF_ERR_INVALID;
+    }
+    if (batch == 0) return MPCCBF_OK;
+    if (n > kMaxN) {
+        set_error("mpccbf_solve_qp_dense_noalloc: n > 128 decision variables is not supported by the one-CTA-per-QP kernel");
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    // scratch: [batch][n*n] scaled P~, then (256-byte aligned) [batch][m*(n|1)] scaled A if it does not fit in shared memory
+    const size_t B = static_cast<size_t>(batch);
+    const size_t nP = (B * n * n + 31) / 32 * 32;
+    const size_t nA = dense_qp_needs_wsA(n, m) ? B * m * (n | 1) : 0;
+    if (nP + nA > kNoAllocDoubles) {
+        set_error("mpccbf_solve_qp_dense_noalloc: batch * n * n (+ batch * m * (n|1) when A does not fit in shared memory) = " +
+                  std::to_string(nP + nA) + " doubles of scratch exceed the fixed " + std::to_string(kNoAllocDoubles) +
+                  " (MPCCBF_NOALLOC_SCRATCH_BYTES); split the batch or use mpccbf_solve_qp_dense");
+        return MPCCBF_ERR_UNSUPPORTED;
+    }
+    double* scratch = nullptr;
+    int rc = noalloc_scratch(&scratch);
+    if (rc != MPCCBF_OK) return rc;
+    DenseOpts o;
+    o.max_iter = cfg ? cfg->admm_max_iter : 0;
+    o.check_every = cfg ? cfg->admm_check_every : 0;
+    o.eps = cfg ? cfg->admm_eps : 0.0;
+    o.rho = cfg ? cfg->admm_rho : 0.0;
+    o.sigma = cfg ? cfg->admm_sigma : 0.0;
+    o.sm_count = 0;
+    o.stream = static_cast<cudaStream_t>(cuda_stream);
+    cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(double) * (nP + nA), o.stream);
+    if (e != cudaSuccess) {
+        set_error(std::string("mpccbf_solve_qp_dense_noalloc: cudaMemsetAsync: ") + cudaGetErrorString(e));
+        return MPCCBF_ERR_CUDA;
+    }
+    return dense_qp_solve_device(o, batch, n, m, P, q, A, l, u, scratch, nA ? scratch + nP : nullptr, x, objective, status, iters);
+}
