@@ -35,6 +35,17 @@ namespace mpccbf {
 #define MPCCBF_HD __host__ __device__ __forceinline__
 #endif
 
+// Reciprocal and reciprocal square root of the active-set step. On the device a / b compiles to a CALLED division
+// routine (~35 instructions and spills around the call); rcp.rn.f64 and rsqrt stay inline. The quotients formed with
+// them are within 1 ulp of the correctly rounded ones, which the iteration does not depend on.
+#ifdef __CUDA_ARCH__
+#define GI_RCP(x) __drcp_rn(x)
+#define GI_RSQRT(x) rsqrt(x)
+#else
+#define GI_RCP(x) (1.0 / (x))
+#define GI_RSQRT(x) (1.0 / std::sqrt(x))
+#endif
+
 // Divergence guard. The iterate of the dual method is the minimiser over a SUBSET of the rows, so its distance to v0
 // never exceeds that of the true minimiser; the bound rows confine every feasible v to a ball of a radius comparable
 // to |v0|. An iterate beyond vmax2 = 1e14 (1 + |v0|^2) therefore proves infeasibility — and it is where a step along an
@@ -136,7 +147,7 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
         for (;;) {
             if (++n_iter > max_iter) return MPCCBF_STATUS_ERROR;
             // ---- Q R = active normals (MGS), d1 = Q' n+, z = n+ - Q d1 ---------------------------------
-            double Q[D][D], R[D][D], d1[D], z[D];
+            double Q[D][D], R[D][D], Rinv[D], d1[D], z[D];
 #pragma unroll
             for (int i = 0; i < D; ++i) z[i] = np[i];
             double dall = 0.0;
@@ -160,8 +171,8 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
                     double nn = 0.0;
 #pragma unroll
                     for (int i = 0; i < D; ++i) nn = fma(w[i], w[i], nn);
-                    const double nrm = sqrt(nn), inv = 1.0 / nrm;
-                    R[c][c] = nrm;
+                    const double inv = GI_RSQRT(nn);   // nn = 0 (dependent normal): inf, as 1 / sqrt(0) before
+                    Rinv[c] = inv;
 #pragma unroll
                     for (int i = 0; i < D; ++i) Q[i][c] = w[i] * inv;
                     // projection of the entering normal (z is already orthogonal to the earlier columns)
@@ -195,25 +206,27 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
 #pragma unroll
                 for (int k = i + 1; k < D; ++k)
                     if (k < g.q) s = fma(-R[i][k], rr[k], s);
-                rr[i] = (i < g.q) ? s / R[i][i] : 0.0;
+                rr[i] = (i < g.q) ? s * Rinv[i] : 0.0;
             }
             const double zt = 1e4 * 2.220446049250313e-16;
             const bool z_zero = !(ztn > zt * zt * dall);
-            double t1 = kInfD;
+            // ratio test min_j u_j / rr_j over rr_j > 0 by cross-multiplication (u_j >= 0): one reciprocal at the end
+            double t1 = kInfD, un = 0.0, rd = 0.0;
             int lpos = -1;
 #pragma unroll
             for (int j = 0; j < D; ++j)
                 if (j < g.q && rr[j] > 0.0) {
-                    const double t = g.u[j] / rr[j];
-                    if (t < t1) {
-                        t1 = t;
+                    if (lpos < 0 || g.u[j] * rd < un * rr[j]) {
+                        un = g.u[j];
+                        rd = rr[j];
                         lpos = j;
                     }
                 }
+            if (lpos >= 0) t1 = un * GI_RCP(rd);
             double sp = -rhs;
 #pragma unroll
             for (int i = 0; i < D; ++i) sp = fma(np[i], g.v[i], sp);
-            const double t2 = z_zero ? kInfD : (-sp / ztn);
+            const double t2 = z_zero ? kInfD : (-sp * GI_RCP(ztn));
             // third rule: a group's multiplier sum reaches its weight
             double t3 = kInfD;
             int g3 = -1;

@@ -585,7 +585,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         double c0_unused;
         unconstrained_minimiser<false>(T, a, g, s, c, v0, c0_unused);
     }
-    const float kinv = static_cast<float>((K - 1) / c.scn[4 * (K - 1)]);
+    const float kinv = static_cast<float>(c.scn[3]);  // (K - 1) / t_{K-1}
     int total_iter = 0;
     // ---- yaw: 2-dof projection, shared by every IMPC iteration --------------------------------
     typename GICore<2, CORE>::State gy;
@@ -838,7 +838,7 @@ MPCCBF_HD void unconstrained_minimiser(const DevTables& T, const StepArgs& a, in
 }
 
 // lim[axis] = {midA, halfA, midV, halfV (of the thresholded bounds), loA, hiA, loV, hiV}; scn[k] = {t_k, inv_norm of the
-// acceleration row, inv_norm of the velocity row, 0} with 1e300 standing for "row independent of v"
+// acceleration row, inv_norm of the velocity row, 0} with 1e300 standing for "row independent of v"; scn[3] = (K - 1) / t_{K-1}
 __host__ __device__ inline void fill_scan_tables(const DevTables& T, const double* tm, double* lim, double* scn, int tid, int nthr) {
     for (int i = tid; i < 6; i += nthr) {
         const int axis = i >> 1, dsel = i & 1;
@@ -852,7 +852,7 @@ __host__ __device__ inline void fill_scan_tables(const DevTables& T, const doubl
         scn[4 * k + 0] = tm[(2 * T.K + k) * kTmplStride + 5];
         scn[4 * k + 1] = fmin(tm[(2 * T.K + k) * kTmplStride + 4], 1e300);
         scn[4 * k + 2] = fmin(tm[(1 * T.K + k) * kTmplStride + 4], 1e300);
-        scn[4 * k + 3] = 0.0;
+        scn[4 * k + 3] = (k == 0) ? (T.K - 1) / tm[(2 * T.K + T.K - 1) * kTmplStride + 5] : 0.0;  // [3]: sample index per unit time
     }
 }
 
@@ -1086,8 +1086,18 @@ static ThreadKernel pick_kernel(const DevTables& T) {
     return impc_thread_kernel_r144<false, false, CORE, 0>;
 }
 
+#ifdef MPCCBF_WITH_R1
+namespace r1 { int launch_impc_thread_r1(const DevTables& T, const StepArgs& a, int sm_count, cudaStream_t stream); }
+#endif
+
 int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cudaStream_t stream) {
     if (a.num_qp <= 0) return cudaSuccess;
+#ifdef MPCCBF_WITH_R1
+    {   // experiment builds only: the round-1 kernel on the same inputs (MPCCBF_THREAD_CORE=9)
+        static const bool use_r1 = [] { const char* e = std::getenv("MPCCBF_THREAD_CORE"); return e && std::atoi(e) == 9; }();
+        if (use_r1 && !T.slack && !T.conn_mode && a.ctrl_pts) return r1::launch_impc_thread_r1(T, a, sm_count, stream);
+    }
+#endif
     if (T.slack && !a.lead_ws) return cudaErrorInvalidValue;
     if (T.conn_mode && (!a.lambda2 || !a.fiedler)) return cudaErrorInvalidValue;
     // Active-set core and launch shape: measured defaults (profiles/r2*_variants.md); MPCCBF_THREAD_CORE = 0 / 1 and
