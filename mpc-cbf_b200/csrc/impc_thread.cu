@@ -33,9 +33,25 @@ namespace mpccbf {
 #ifndef MPCCBF_THREAD_CFG
 #define MPCCBF_THREAD_CFG 0
 #endif
-constexpr int kCandMax = 32;   // candidate safety rows kept per agent (more: scan all rows)
+#ifndef MPCCBF_CAND_MAX
+#define MPCCBF_CAND_MAX 32
+#endif
+constexpr int kCandMax = MPCCBF_CAND_MAX;   // candidate safety rows kept per agent (more: scan all rows)
 constexpr int kSolStride = 7;  // per-agent result record: v[6] (whitened free dof of the last successful iterate), n_ok
 constexpr int kSnapD = 8, kSnapI = 5;  // stage-A snapshot per agent: v[4], u[4] | id[4], q
+// Per-agent scratch is LANE-STRIDED: element i of an array belongs to lane l at [i * kLS + l] (doubles; the snapshot's ints
+// sit in 8-byte slots, kLSI ints apart), and the arrays of a warp follow each other at compile-time offsets, so every
+// access is one per-thread base plus an immediate (the tests' host build uses the same layout with lane 0).
+constexpr int kLS = 32, kLSI = 64;
+constexpr int kRow = kLS * 8;                          // bytes of one lane-strided row
+constexpr int kOffSol = 0;
+constexpr int kOffSnapD = kOffSol + kSolStride * kRow;
+constexpr int kOffSnapI = kOffSnapD + kSnapD * kRow;
+constexpr int kOffCand = kOffSnapI + kSnapI * kRow;    // kCandMax rows of kLS unsigned shorts
+constexpr int kOffPred = kOffCand + kCandMax * kLS * 2;  // H * 4 rows; then (conn_mode) H * 3 rows, Fiedler vectors; scenario states
+// CTA-shared tables at compile-time offsets from the start of shared memory (doubles): pq[5][4], lim[3][8], scn[K][4];
+// the horizon-sized tables follow (ThreadSmemLayout)
+constexpr int kOffLim = 20, kOffScn = 44;
 
 #ifdef __CUDA_ARCH__
 #define TLDG(p) __ldg(p)
@@ -292,15 +308,13 @@ struct RowsXY {
     double tol;
     // safety rows
     const double* st;     // scenario states (shared memory) [N][6]
-    const double* pred;   // ego states per horizon step: pred[(k*4 + c) * pstride], c = px,py,vx,vy
-    const unsigned short* cand;  // candidate row ids: cand[i * cstride]
-    int pstride, cstride;
+    const double* pred;   // ego states per horizon step: pred[(k*4 + c) * kLS], c = px,py,vx,vy
+    const unsigned short* cand;  // candidate row ids: cand[i * kLS]
     int ncand;            // < 0: scan all `ncbf` rows
     int ncbf, hit, self;  // ncbf pairwise rows: [0, nsafe) safety HOCBF, [nsafe, ncbf) distance CLF (conn_mode, lambda2 <= 0.1)
     int nsafe;            // (N - 1) * hit
     int nconn;            // connectivity HOCBF rows (conn_mode, lambda2 > 0.1): row ids ncbf + k, values in conn[]
-    const double* conn;   // conn[(k * 3 + i) * cnstride] = (gx, gy, b) of horizon step k
-    int cnstride;
+    const double* conn;   // conn[(k * 3 + i) * kLS] = (gx, gy, b) of horizon step k
     double dmin2, gamma;
     int nid_fix;          // 8K
     const double (*pq)[4];  // polynomial row structure (DevTables::poly)
@@ -316,9 +330,9 @@ struct RowsXY {
         if constexpr (CONN) {
             if (j >= ncbf) {  // connectivity HOCBF row of horizon step j - ncbf (computed once per IMPC iteration)
                 k = j - ncbf;
-                ax = conn[(k * 3) * cnstride];
-                ay = conn[(k * 3 + 1) * cnstride];
-                b = conn[(k * 3 + 2) * cnstride];
+                ax = conn[(k * 3) * kLS];
+                ay = conn[(k * 3 + 1) * kLS];
+                b = conn[(k * 3 + 2) * kLS];
                 return;
             }
         }
@@ -333,11 +347,11 @@ struct RowsXY {
         k = jj - nb * hit;
         const int other = nb + (nb >= self ? 1 : 0);
         const double* o = st + other * 6;
-        const double* e = pred + (k * 4) * pstride;
+        const double* e = pred + (k * 4) * kLS;
         if (clf)
-            clf_row_lifted(e[0], e[pstride], e[2 * pstride], e[3 * pstride], o[0], o[1], ax, ay, b);
+            clf_row_lifted(e[0], e[kLS], e[2 * kLS], e[3 * kLS], o[0], o[1], ax, ay, b);
         else
-            hocbf_row(e[0], e[pstride], e[2 * pstride], e[3 * pstride], o[0], o[1], o[3], o[4], dmin2, gamma, ax, ay, b);
+            hocbf_row(e[0], e[kLS], e[2 * kLS], e[3 * kLS], o[0], o[1], o[3], o[4], dmin2, gamma, ax, ay, b);
     }
     // g(v) = rhs - n.v of safety row j: positive when violated
     MPCCBF_HD double cbf_g(const double (&v)[4], double ax, double ay, double b, int k) const {
@@ -406,7 +420,7 @@ struct RowsXY {
         if (ncand < 0) {
             for (int j = 0; j < ncbf; ++j) check_cbf(j, v, kb, jb);
         } else {
-            for (int i = 0; i < ncand; ++i) check_cbf(cand[i * cstride], v, kb, jb);
+            for (int i = 0; i < ncand; ++i) check_cbf(cand[i * kLS], v, kb, jb);
         }
         if constexpr (CONN)
             for (int k = 0; k < nconn; ++k) check_cbf(ncbf + k, v, kb, jb);
@@ -505,25 +519,22 @@ struct AgentCtx {
     const double* scn;                // [K][4] key-scan table {t_k, inv_norm_acc, inv_norm_vel, -}
     const double* lim;                // [3 axes][8]: mid / half of the thresholded bounds, raw lo / hi
     const double* st;                 // this agent's scenario states [N][6]
-    double* pred;                     // [(k*4 + c) * pstride]
-    unsigned short* cand;             // [i * cstride]
-    int pstride, cstride;
-    double* sol;                      // [kSolStride] result record of this agent
-    double* snapd;                    // [kSnapD * sstride] stage-A snapshot (doubles), snapi (ints)
+    double* pred;                     // [(k*4 + c) * kLS]
+    unsigned short* cand;             // [i * kLS]
+    double* sol;                      // [kSolStride * kLS] result record of this agent
+    double* snapd;                    // [kSnapD * kLS] stage-A snapshot (doubles), snapi [kSnapI * kLSI] (ints)
     int* snapi;
-    int sstride;
     unsigned char* lead;              // [N-1] group leaders of this agent (slack mode), else NULL
     // conn_mode: algebraic connectivity and Fiedler vector of this agent's scenario, scratch for its connectivity rows
     double lam2;
     const double* fied;
-    double* conn;                     // [(k * 3 + i) * cnstride]
-    int cnstride;
+    double* conn;                     // [(k * 3 + i) * kLS]
 };
 
 // keeps the safety rows that can be violated somewhere inside the acceleration box (a row that
 // holds on the whole box holds at every point the bound rows admit, so dropping it is exact)
 template <bool SOFT, bool CONN>
-MPCCBF_HD void build_candidates(RowsXY<SOFT, CONN>& rx, const DevTables& T, unsigned short* cand, int cstride, unsigned long long& k0mask,
+MPCCBF_HD void build_candidates(RowsXY<SOFT, CONN>& rx, const DevTables& T, unsigned short* cand, unsigned long long& k0mask,
                                  bool& k0valid) {
     // The predicted ego state at t_0 = 0 is the current state (the curve is pinned there by the initial-state rows), so
     // the k = 0 safety row of neighbour nb is the same row in every IMPC iteration: its candidate test is done once
@@ -548,7 +559,7 @@ MPCCBF_HD void build_candidates(RowsXY<SOFT, CONN>& rx, const DevTables& T, unsi
             if (fill && keep && j < rx.nsafe) k0mask |= 1ull << j;
         }
         if (keep) {
-            if (nc < kCandMax) cand[nc * cstride] = static_cast<unsigned short>(j);
+            if (nc < kCandMax) cand[nc * kLS] = static_cast<unsigned short>(j);
             ++nc;
         }
     }
@@ -618,14 +629,11 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     rx.st = c.st;
     rx.pred = c.pred;
     rx.cand = c.cand;
-    rx.pstride = c.pstride;
-    rx.cstride = c.cstride;
     rx.ncand = 0;
     rx.ncbf = 0;
     rx.nsafe = 0;
     rx.nconn = 0;
     rx.conn = c.conn;
-    rx.cnstride = c.cnstride;
     rx.hit = 1;
     rx.self = self;
     rx.dmin2 = T.dmin2;
@@ -673,9 +681,9 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                 const int hit = (it == 0) ? 1 : H;
                 if (it == 0) {
                     c.pred[0] = s[0][0];
-                    c.pred[c.pstride] = s[1][0];
-                    c.pred[2 * c.pstride] = s[0][1];
-                    c.pred[3 * c.pstride] = s[1][1];
+                    c.pred[kLS] = s[1][0];
+                    c.pred[2 * kLS] = s[0][1];
+                    c.pred[3 * kLS] = s[1][1];
                 } else {
                     for (int k = 0; k < H; ++k) {
 #pragma unroll
@@ -683,7 +691,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                             const double* t = c.tm + (d * K + k) * kTmplStride;
 #pragma unroll
                             for (int ax = 0; ax < 2; ++ax)
-                                c.pred[(k * 4 + d * 2 + ax) * c.pstride] =
+                                c.pred[(k * 4 + d * 2 + ax) * kLS] =
                                     fma(t[0], gx.v[2 * ax], fma(t[1], gx.v[2 * ax + 1], fma(t[2], s[ax][0], t[3] * s[ax][1])));
                         }
                     }
@@ -691,12 +699,12 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                 if (dirty) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        gx.v[i] = c.snapd[i * c.sstride];
-                        gx.u[i] = c.snapd[(4 + i) * c.sstride];
-                        gx.id[i] = c.snapi[i * c.sstride];
+                        gx.v[i] = c.snapd[i * kLS];
+                        gx.u[i] = c.snapd[(4 + i) * kLS];
+                        gx.id[i] = c.snapi[i * kLSI];
                         if constexpr (SOFT) gs.grp[i] = -1;
                     }
-                    gx.q = c.snapi[4 * c.sstride];
+                    gx.q = c.snapi[4 * kLSI];
                     GICore<4, CORE>::refactor(gx, rx);
                 }
                 dirty = false;
@@ -709,12 +717,12 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                         if (c.lam2 > 0.1) {
                             for (int k = 0; k < hit; ++k) {
                                 double gx2, gy2, bb;
-                                conn_row_lifted(c.st, N, self, c.fied, c.lam2, T.dmax, T.gamma, c.pred[(k * 4) * c.pstride],
-                                                c.pred[(k * 4 + 1) * c.pstride], c.pred[(k * 4 + 2) * c.pstride],
-                                                c.pred[(k * 4 + 3) * c.pstride], gx2, gy2, bb);
-                                c.conn[(k * 3) * c.cnstride] = gx2;
-                                c.conn[(k * 3 + 1) * c.cnstride] = gy2;
-                                c.conn[(k * 3 + 2) * c.cnstride] = bb;
+                                conn_row_lifted(c.st, N, self, c.fied, c.lam2, T.dmax, T.gamma, c.pred[(k * 4) * kLS],
+                                                c.pred[(k * 4 + 1) * kLS], c.pred[(k * 4 + 2) * kLS],
+                                                c.pred[(k * 4 + 3) * kLS], gx2, gy2, bb);
+                                c.conn[(k * 3) * kLS] = gx2;
+                                c.conn[(k * 3 + 1) * kLS] = gy2;
+                                c.conn[(k * 3 + 2) * kLS] = bb;
                             }
                             rx.nconn = hit;
                         } else {
@@ -724,7 +732,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                 }
                 if constexpr (SOFT)
                     for (int nb = 0; nb < N - 1; ++nb) c.lead[nb] = 0;
-                build_candidates<SOFT, CONN>(rx, T, c.cand, c.cstride, k0mask, k0valid);
+                build_candidates<SOFT, CONN>(rx, T, c.cand, k0mask, k0valid);
                 run = rx.ncand != 0 || rx.nconn > 0;
             } else {
                 run = true;
@@ -738,11 +746,11 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
             it_iter += total_iter;  // yaw iterations are booked on IMPC iteration 0
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                c.snapd[i * c.sstride] = gx.v[i];
-                c.snapd[(4 + i) * c.sstride] = gx.u[i];
-                c.snapi[i * c.sstride] = gx.id[i];
+                c.snapd[i * kLS] = gx.v[i];
+                c.snapd[(4 + i) * kLS] = gx.u[i];
+                c.snapi[i * kLSI] = gx.id[i];
             }
-            c.snapi[4 * c.sstride] = gx.q;
+            c.snapi[4 * kLSI] = gx.q;
             mode = kIter;
             continue;
         }
@@ -759,16 +767,16 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         }
         ++n_ok;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) c.sol[i] = gx.v[i];
-        c.sol[4] = gy.v[0];
-        c.sol[5] = gy.v[1];
+        for (int i = 0; i < 4; ++i) c.sol[i * kLS] = gx.v[i];
+        c.sol[4 * kLS] = gy.v[0];
+        c.sol[5 * kLS] = gy.v[1];
         if constexpr (SOFT) pen_last = (run && a.objective) ? rx.penalty(gx.v) : 0.0;
         if (a.ctrl_all) {  // every iterate (mpccbf_optimize_one): small batches, direct stores
             double* out = a.ctrl_all + (sbase + it) * T.n;
             for (int i = 0; i < T.n; ++i) {
                 const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
                 const int ax = rem / T.c, cp = rem - ax * T.c;
-                out[i] = ctrl_point(c.yw + (piece * T.c + cp) * 4, c.st[self * 6 + ax], c.st[self * 6 + 3 + ax], c.sol[2 * ax], c.sol[2 * ax + 1]);
+                out[i] = ctrl_point(c.yw + (piece * T.c + cp) * 4, c.st[self * 6 + ax], c.st[self * 6 + 3 + ax], c.sol[2 * ax * kLS], c.sol[(2 * ax + 1) * kLS]);
             }
         }
         ++it;
@@ -776,9 +784,9 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     // ---- result record (expanded to control points cooperatively by the warp) ------------------
     if (n_ok == 0) {
 #pragma unroll
-        for (int i = 0; i < 6; ++i) c.sol[i] = 0.0;
+        for (int i = 0; i < 6; ++i) c.sol[i * kLS] = 0.0;
     }
-    c.sol[6] = static_cast<double>(n_ok);
+    c.sol[6 * kLS] = static_cast<double>(n_ok);
     if (a.n_curves) a.n_curves[g] = n_ok;
     if (a.objective) {
         double obj = 0.0;
@@ -788,7 +796,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
             double dd = 0.0, nn = 0.0;
 #pragma unroll
             for (int i = 0; i < 6; ++i) {
-                const double e = c.sol[i] - v0[i];
+                const double e = c.sol[i * kLS] - v0[i];
                 dd = fma(e, e, dd);
                 nn = fma(v0[i], v0[i], nn);
             }
@@ -857,32 +865,37 @@ __host__ __device__ inline void fill_scan_tables(const DevTables& T, const doubl
 }
 
 struct ThreadSmemLayout {
-    int tm, yw, vr, kr, vq, omap_bytes;  // doubles (omap in bytes), CTA-shared
-    int st, pred, sol, snapd, snapi_bytes, cand_bytes;   // per warp: doubles (snapi, cand in bytes)
-    int fied, conn;                  // per warp (conn_mode only): Fiedler vectors of the tile's scenarios, connectivity rows
+    // CTA-shared tables (doubles from the start of shared memory): pq, lim, scn at the compile-time offsets 0 / kOffLim /
+    // kOffScn, then tm [3][K][kTmplStride], vr [2][K], kr [2][K], yw [m1][4], omap (unsigned shorts)
+    int off_tm, off_vr, off_kr, off_yw, off_omap;
+    int n_tm, n_yw, n_vr;
+    // per warp (bytes from the warp's block): the fixed-offset arrays (kOffSol .. kOffPred), then
+    int off_conn, off_fied, off_st;  // conn_mode rows and Fiedler vectors (empty otherwise), scenario states
+    int n_fied;
     int nscen_max;
-    size_t shared_bytes, warp_bytes;
+    int shared_bytes, warp_bytes;
 };
 
 static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count) {
     ThreadSmemLayout L;
-    L.tm = 3 * T.K * kTmplStride;
-    L.yw = T.m1 * 4;
-    L.vr = 2 * T.K;
-    L.kr = 2 * T.K;
-    L.vq = 20 + 24 + 4 * T.K;  // pq, lim[3][8], scn[K][4]
-    L.omap_bytes = ((T.n * 2 + 15) / 16) * 16;
-    L.nscen_max = (32 - 1) / std::max(agent_count, 1) + 2;
-    L.st = L.nscen_max * T.N * 6;
-    L.pred = std::max(T.H, 1) * 4 * 32;
-    L.sol = 32 * kSolStride;
-    L.snapd = 32 * kSnapD;
-    L.snapi_bytes = 32 * kSnapI * 4;
-    L.cand_bytes = kCandMax * 32 * 2;
-    L.shared_bytes = sizeof(double) * (L.tm + L.yw + L.vr + L.kr + L.vq) + L.omap_bytes;
-    L.fied = T.conn_mode ? L.nscen_max * T.N : 0;
-    L.conn = T.conn_mode ? std::max(T.H, 1) * 3 * 32 : 0;
-    L.warp_bytes = sizeof(double) * (L.st + L.pred + L.sol + L.snapd + L.fied + L.conn) + L.snapi_bytes + L.cand_bytes;
+    L.n_tm = 3 * T.K * kTmplStride;
+    L.n_vr = 2 * T.K;
+    L.n_yw = T.m1 * 4;
+    L.off_tm = kOffScn + 4 * T.K;
+    L.off_vr = L.off_tm + L.n_tm;
+    L.off_kr = L.off_vr + L.n_vr;
+    L.off_yw = L.off_kr + L.n_vr;
+    L.off_omap = L.off_yw + L.n_yw;
+    L.shared_bytes = (8 * L.off_omap + T.n * 2 + 15) / 16 * 16;
+    // scenarios a tile of 32 consecutive agents can touch
+    const int ac = std::max(agent_count, 1);
+    L.nscen_max = (32 % ac == 0) ? 32 / ac : (ac % 32 == 0 ? 1 : (32 - 1) / ac + 2);
+    const int H = std::max(T.H, 1);
+    L.off_conn = kOffPred + H * 4 * kRow;
+    L.off_fied = L.off_conn + (T.conn_mode ? H * 3 * kRow : 0);
+    L.n_fied = T.conn_mode ? L.nscen_max * T.N : 0;
+    L.off_st = (L.off_fied + 8 * L.n_fied + 15) / 16 * 16;
+    L.warp_bytes = (L.off_st + 8 * L.nscen_max * T.N * 6 + 15) / 16 * 16;
     return L;
 }
 
@@ -893,6 +906,7 @@ template <int CFG> struct ThreadCfg;
 template <> struct ThreadCfg<0> { static constexpr int kThreads = 128, kCtas = 4; };
 template <> struct ThreadCfg<1> { static constexpr int kThreads = 448, kCtas = 1; };
 template <> struct ThreadCfg<2> { static constexpr int kThreads = 224, kCtas = 2; };
+template <> struct ThreadCfg<3> { static constexpr int kThreads = 64, kCtas = 7; };
 
 // ptxas derives 128 registers from __launch_bounds__(448, 1) and (224, 2) alike (it budgets for 512 threads), although
 // 14 warps x 32 x 144 registers fit the 64 K register file: shapes 1 and 2 state their budget with __maxnreg__ instead.
@@ -913,30 +927,26 @@ impc_thread_kernel_r144(const __grid_constant__ DevTables T, const __grid_consta
 template <bool SOFT, bool CONN, int CORE>
 __device__ __forceinline__ void thread_kernel_body(const DevTables& T, const StepArgs& a, const ThreadSmemLayout& L) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double* tm = reinterpret_cast<double*>(smem_raw);
-    double* yw = tm + L.tm;
-    double* vr = yw + L.yw;
-    double* kr = vr + L.vr;
-    double* svq = kr + L.kr;
-    unsigned short* omap = reinterpret_cast<unsigned short*>(svq + L.vq);
-    unsigned char* wbase = smem_raw + L.shared_bytes + static_cast<size_t>(threadIdx.x >> 5) * L.warp_bytes;
-    double* wst = reinterpret_cast<double*>(wbase);
-    double* wpred = wst + L.st;
-    double* wsol = wpred + L.pred;
-    double* wsnapd = wsol + L.sol;
-    double* wfied = wsnapd + L.snapd;
-    double* wconn = wfied + L.fied;
-    int* wsnapi = reinterpret_cast<int*>(wconn + L.conn);
-    unsigned short* wcand = reinterpret_cast<unsigned short*>(reinterpret_cast<unsigned char*>(wsnapi) + L.snapi_bytes);
+    double* svq = reinterpret_cast<double*>(smem_raw);   // pq | lim | scn at compile-time offsets
+    double* tm = svq + L.off_tm;
+    double* vr = svq + L.off_vr;
+    double* kr = svq + L.off_kr;
+    double* yw = svq + L.off_yw;
+    unsigned short* omap = reinterpret_cast<unsigned short*>(svq + L.off_omap);
+    unsigned char* wbase = smem_raw + L.shared_bytes + (threadIdx.x >> 5) * L.warp_bytes;
+    double* wsol = reinterpret_cast<double*>(wbase + kOffSol);
+    double* wfied = reinterpret_cast<double*>(wbase + L.off_fied);
+    double* wst = reinterpret_cast<double*>(wbase + L.off_st);
 
-    for (int i = threadIdx.x; i < L.tm; i += blockDim.x) tm[i] = T.tmpl[i];
-    for (int i = threadIdx.x; i < L.yw; i += blockDim.x) yw[i] = T.yw[i];
-    for (int i = threadIdx.x; i < L.vr; i += blockDim.x) {
+    for (int i = threadIdx.x; i < L.n_tm; i += blockDim.x) tm[i] = T.tmpl[i];
+    for (int i = threadIdx.x; i < L.n_yw; i += blockDim.x) yw[i] = T.yw[i];
+    for (int i = threadIdx.x; i < L.n_vr; i += blockDim.x) {
         vr[i] = T.Vr[i];
         kr[i] = T.Kr[i];
     }
     if (threadIdx.x < 20) svq[threadIdx.x] = T.pq[threadIdx.x >> 2][threadIdx.x & 3];
-    fill_scan_tables(T, tm, svq + 20, svq + 44, threadIdx.x, blockDim.x);
+    __syncthreads();   // fill_scan_tables reads tm
+    fill_scan_tables(T, tm, svq + kOffLim, svq + kOffScn, threadIdx.x, blockDim.x);
     for (int i = threadIdx.x; i < T.n; i += blockDim.x) {
         const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
         const int ax = rem / T.c, cp = rem - ax * T.c;
@@ -961,7 +971,7 @@ __device__ __forceinline__ void thread_kernel_body(const DevTables& T, const Ste
             double2* dst = reinterpret_cast<double2*>(wst);
             const int words = (s_hi - s_lo + 1) * N * 3;
             for (int i = lane; i < words; i += 32) dst[i] = __ldg(src + i);
-            if (L.fied)
+            if (L.n_fied)
                 for (int i = lane; i < (s_hi - s_lo + 1) * N; i += 32) wfied[i] = __ldg(a.fiedler + static_cast<size_t>(s_lo) * N + i);
         }
         __syncwarp();
@@ -972,21 +982,18 @@ __device__ __forceinline__ void thread_kernel_body(const DevTables& T, const Ste
             AgentCtx c;
             c.tm = tm; c.yw = yw; c.vr = vr; c.kr = kr;
             c.pq = reinterpret_cast<const double (*)[4]>(svq);
-            c.lim = svq + 20;
-            c.scn = svq + 44;
+            c.lim = svq + kOffLim;
+            c.scn = svq + kOffScn;
             c.st = wst + (scen - s_lo) * N * 6;
-            c.pred = wpred + lane;
-            c.pstride = 32;
-            c.cand = wcand + lane;
-            c.cstride = 32;
-            c.sol = wsol + lane * kSolStride;
-            c.snapd = wsnapd + lane;
-            c.snapi = wsnapi + lane;
-            c.sstride = 32;
-            c.lam2 = L.fied ? __ldg(a.lambda2 + scen) : 0.0;
+            unsigned char* tb = wbase + lane * 8;   // every lane-strided array of this agent: tb + immediate
+            c.sol = reinterpret_cast<double*>(tb + kOffSol);
+            c.snapd = reinterpret_cast<double*>(tb + kOffSnapD);
+            c.snapi = reinterpret_cast<int*>(tb + kOffSnapI);
+            c.cand = reinterpret_cast<unsigned short*>(wbase + kOffCand) + lane;
+            c.pred = reinterpret_cast<double*>(tb + kOffPred);
+            c.conn = reinterpret_cast<double*>(tb + L.off_conn);
+            c.lam2 = L.n_fied ? __ldg(a.lambda2 + scen) : 0.0;
             c.fied = wfied + (scen - s_lo) * N;
-            c.conn = wconn + lane;
-            c.cnstride = 32;
             c.lead = SOFT ? a.lead_ws + static_cast<size_t>(g) * (N - 1) : nullptr;
             agent_thread<SOFT, CONN, CORE>(T, a, g, self, c);
         }
@@ -995,24 +1002,30 @@ __device__ __forceinline__ void thread_kernel_body(const DevTables& T, const Ste
             double* vo = a.v_out + static_cast<size_t>(g0) * 6;
             for (int idx = lane; idx < cnt * 6; idx += 32) {
                 const int ag = __float2int_rz((idx + 0.5f) * (1.0f / 6.0f)), i = idx - ag * 6;
-                vo[idx] = wsol[ag * kSolStride + i];   // zeros when the agent has no curve
+                vo[idx] = wsol[i * kLS + ag];   // zeros when the agent has no curve
             }
         }
         if (a.ctrl_pts) {   // control points of the last successful iterate: coalesced stores, whole warp
+            // one agent after the other (its state, record and scenario are warp-uniform); lane l owns the control
+            // points l, l + 32, ... of every agent, so their table entries are looked up once per tile
             double* out = a.ctrl_pts + static_cast<size_t>(g0) * n;
-            const int total = cnt * n;
-            const float inv_n = 1.0f / static_cast<float>(n);
-            // the tile's agents in order: scenario / agent-in-scenario advance without a division per element
-            for (int idx = lane; idx < total; idx += 32) {
-                const int ag = __float2int_rz((idx + 0.5f) * inv_n), i = idx - ag * n;   // exact: idx < 32 n
-                const double* rec = wsol + ag * kSolStride;
-                const int gg = g0 + ag;
-                int sc = s_lo;                                   // a tile spans at most nscen_max scenarios
-                while ((sc + 1) * a.agent_count <= gg) ++sc;
-                const double* sta = wst + ((sc - s_lo) * N + a.agent_begin + (gg - sc * a.agent_count)) * 6;
-                const unsigned m = omap[i];
+            int sc = s_lo, a0 = g0 - s_lo * a.agent_count;   // scenario and agent-in-shard of the tile's first agent
+            for (int i0 = 0; i0 < n; i0 += 32) {
+                const int i = i0 + lane;
+                const unsigned m = omap[min(i, n - 1)];
                 const int ax = m & 3;
-                out[idx] = (rec[6] > 0.0) ? ctrl_point(yw + (m >> 2) * 4, sta[ax], sta[3 + ax], rec[2 * ax], rec[2 * ax + 1]) : 0.0;
+                const double* y = yw + (m >> 2) * 4;
+                const double y0 = y[0], y1 = y[1], y2 = y[2], y3 = y[3];
+                int scc = sc, aa = a0;
+                for (int ag = 0; ag < cnt; ++ag) {
+                    const double* sta = wst + ((scc - s_lo) * N + a.agent_begin + aa) * 6;
+                    const double val = fma(y0, sta[ax], fma(y1, sta[3 + ax], fma(y2, wsol[(2 * ax) * kLS + ag], y3 * wsol[(2 * ax + 1) * kLS + ag])));
+                    if (i < n) out[static_cast<size_t>(ag) * n + i] = (wsol[6 * kLS + ag] > 0.0) ? val : 0.0;
+                    if (++aa == a.agent_count) {
+                        aa = 0;
+                        ++scc;
+                    }
+                }
             }
         }
         __syncwarp();
@@ -1022,10 +1035,12 @@ __device__ __forceinline__ void thread_kernel_body(const DevTables& T, const Ste
 #ifdef MPCCBF_HOST_EMUL
 // Test-only (tests/emul): the SAME per-agent function on the host, one agent at a time.
 void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
-    std::vector<double> pred(static_cast<size_t>(std::max(T.H, 1)) * 4), sol(kSolStride);
-    std::vector<unsigned short> cand(kCandMax);
-    std::vector<double> snapd(kSnapD), connrows(static_cast<size_t>(std::max(T.H, 1)) * 3);
-    std::vector<int> snapi(kSnapI);
+    // the same lane-strided scratch layout as a warp of the kernel, used by lane 0
+    const int H = std::max(T.H, 1);
+    std::vector<double> pred(static_cast<size_t>(H) * 4 * kLS), sol(static_cast<size_t>(kSolStride) * kLS);
+    std::vector<unsigned short> cand(static_cast<size_t>(kCandMax) * kLS);
+    std::vector<double> snapd(static_cast<size_t>(kSnapD) * kLS), connrows(static_cast<size_t>(H) * 3 * kLS);
+    std::vector<int> snapi(static_cast<size_t>(kSnapI) * kLSI);
     std::vector<double> lim(24), scn(static_cast<size_t>(4) * T.K);
     std::vector<unsigned char> lead(static_cast<size_t>(std::max(T.N, 1)));
     fill_scan_tables(T, T.tmpl, lim.data(), scn.data(), 0, 1);
@@ -1039,17 +1054,13 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
         c.scn = scn.data();
         c.st = a.states + static_cast<size_t>(scen) * T.N * 6;
         c.pred = pred.data();
-        c.pstride = 1;
         c.cand = cand.data();
-        c.cstride = 1;
         c.sol = sol.data();
         c.snapd = snapd.data();
         c.snapi = snapi.data();
-        c.sstride = 1;
         c.lam2 = (T.conn_mode && a.lambda2) ? a.lambda2[scen] : 0.0;
         c.fied = (T.conn_mode && a.fiedler) ? a.fiedler + static_cast<size_t>(scen) * T.N : nullptr;
         c.conn = connrows.data();
-        c.cnstride = 1;
         c.lead = lead.data();
         static const int core = [] { const char* e = std::getenv("MPCCBF_THREAD_CORE"); return e ? std::atoi(e) : MPCCBF_THREAD_CORE; }();
         if (T.slack) {
@@ -1060,12 +1071,12 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
             if (core == 1) agent_thread<false, false, 1>(T, a, g, self, c); else agent_thread<false, false, 0>(T, a, g, self, c);
         }
         if (a.v_out)
-            for (int i = 0; i < 6; ++i) a.v_out[static_cast<size_t>(g) * 6 + i] = sol[i];
+            for (int i = 0; i < 6; ++i) a.v_out[static_cast<size_t>(g) * 6 + i] = sol[i * kLS];
         double* out = a.ctrl_pts + static_cast<size_t>(g) * T.n;
         for (int i = 0; a.ctrl_pts && i < T.n; ++i) {
             const int piece = i / (3 * T.c), rem = i - piece * 3 * T.c;
             const int ax = rem / T.c, cp = rem - ax * T.c;
-            out[i] = (sol[6] > 0.0) ? ctrl_point(T.yw + (piece * T.c + cp) * 4, c.st[self * 6 + ax], c.st[self * 6 + 3 + ax], sol[2 * ax], sol[2 * ax + 1]) : 0.0;
+            out[i] = (sol[6 * kLS] > 0.0) ? ctrl_point(T.yw + (piece * T.c + cp) * 4, c.st[self * 6 + ax], c.st[self * 6 + 3 + ax], sol[2 * ax * kLS], sol[(2 * ax + 1) * kLS]) : 0.0;
         }
     }
 }
@@ -1103,7 +1114,7 @@ int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cuda
     // Active-set core and launch shape: measured defaults (profiles/r2*_variants.md); MPCCBF_THREAD_CORE = 0 / 1 and
     // MPCCBF_THREAD_CFG = 0 / 1 / 2 override them for experiments.
     static const int core = [] { const char* e = std::getenv("MPCCBF_THREAD_CORE"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CORE; return v == 1 ? 1 : 0; }();
-    static const int cfgi = [] { const char* e = std::getenv("MPCCBF_THREAD_CFG"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CFG; return (v == 1 || v == 2) ? v : 0; }();
+    static const int cfgi = [] { const char* e = std::getenv("MPCCBF_THREAD_CFG"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CFG; return (v >= 1 && v <= 3) ? v : 0; }();
     ThreadKernel kern;
     int threads;
     if (cfgi == 1) {
@@ -1112,6 +1123,9 @@ int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cuda
     } else if (cfgi == 2) {
         kern = core ? pick_kernel<1, 2>(T) : pick_kernel<0, 2>(T);
         threads = ThreadCfg<2>::kThreads;
+    } else if (cfgi == 3) {
+        kern = core ? pick_kernel<1, 2>(T) : pick_kernel<0, 2>(T);
+        threads = ThreadCfg<3>::kThreads;
     } else {
         kern = core ? pick_kernel<1, 0>(T) : pick_kernel<0, 0>(T);
         threads = ThreadCfg<0>::kThreads;
