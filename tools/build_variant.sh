@@ -10,7 +10,7 @@ nvcc $ARCH -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xptxas -v "$@" -c -o /tmp/
 grep -A2 "impc_thread_kernelILb0ELb0ELi0ELi0" /tmp/exp/impc_thread_$NAME.log | grep -E "stack|Used" 
 EXTRA=""
 if echo "$@" | grep -q MPCCBF_WITH_R1; then
-  [ -f /tmp/exp/impc_thread_r1.o ] || nvcc $ARCH -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -c -o /tmp/exp/impc_thread_r1.o impc_thread_r1.cu
+  [ -f /tmp/exp/impc_thread_r1.o ] || nvcc $ARCH -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -I. -I../../include -c -o /tmp/exp/impc_thread_r1.o ../../tools/r1_kernel/impc_thread_r1.cu
   EXTRA=/tmp/exp/impc_thread_r1.o
 fi
 OBJS=$(ls build/*.o | grep -v "build/impc_thread.o")
