@@ -658,6 +658,12 @@ def run_b200(args):
 
 if __name__ == "__main__":
     a = parse_args()
+    # Only the JSON line goes to stdout: libraries that print there (NCCL's version banner when a communicator is
+    # created) are sent to stderr by pointing fd 1 at fd 2 and keeping the real stdout for print().
+    sys.stdout.flush()
+    _real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = _real_stdout
     if a.impl == "reference":
         run_reference(a)
     else:
