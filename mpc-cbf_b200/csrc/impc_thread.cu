@@ -667,7 +667,14 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     int n_ok = 0;
     unsigned long long k0mask = 0ull;  // candidate flags of the k = 0 safety rows (same rows in every IMPC iteration)
     bool k0valid = false;
-    bool dirty = false;  // gx has safety rows in its active set (not reusable as stage A)
+    bool dirty = false;  // gx has moved away from the stage-A solution
+    // The rows of IMPC iteration i that exist in iteration i + 1 as well: the bound rows and the k = 0 safety rows (the
+    // predicted state at t_0 is the current state in every iteration). When the active set of a finished iteration holds
+    // only such rows, its (v, multipliers, active set) is a solution pair of a SUB-problem of the next iteration — a
+    // valid starting point of the dual method — so the next iteration continues from it instead of from stage A and
+    // only adds what its new rows (k >= 1, rebuilt at the new predicted states) require. Same minimiser (it is
+    // unique); measured on the bench workload: 4.9 -> ~1 active-set steps in iteration 1.
+    bool reuse = false;
     double pen_last = 0.0;  // slack mode: sum_j w_j s_j of the last successful iterate
     const size_t sbase = static_cast<size_t>(g) * T.iters;
     int mode = kStageA, it = 0, it_iter = 0;
@@ -696,7 +703,18 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                         }
                     }
                 }
-                if (dirty) {
+                if (dirty && reuse) {
+                    // row ids of the k = 0 safety rows in the numbering of this iteration (hit rows per neighbour)
+                    if (rx.hit != hit) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (gx.id[i] >= rx.nid_fix) {
+                                const int j = gx.id[i] - rx.nid_fix;
+                                const int nb = (rx.hit == 1) ? j : ((rx.hit == 2) ? (j >> 1) : j / rx.hit);
+                                gx.id[i] = rx.nid_fix + nb * hit;
+                            }
+                    }
+                } else if (dirty) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         gx.v[i] = c.snapd[i * kLS];
@@ -707,7 +725,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                     gx.q = c.snapi[4 * kLSI];
                     GICore<4, CORE>::refactor(gx, rx);
                 }
-                dirty = false;
+                if (!reuse) dirty = false;
                 rx.hit = hit;
                 rx.nsafe = (N - 1) * hit;
                 rx.ncbf = rx.nsafe;
@@ -754,7 +772,20 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
             mode = kIter;
             continue;
         }
-        dirty = n2 > 0;
+        dirty = dirty || n2 > 0;
+        reuse = false;
+        if constexpr (!SOFT && !CONN && CORE == 0) {
+            if (dirty && stat == MPCCBF_STATUS_OPTIMAL) {
+                reuse = true;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (i < gx.q && gx.id[i] >= rx.nid_fix) {
+                        const int j = gx.id[i] - rx.nid_fix;
+                        const int k = (rx.hit == 1) ? 0 : ((rx.hit == 2) ? (j & 1) : j % rx.hit);
+                        if (k != 0) reuse = false;
+                    }
+            }
+        }
         a.status[sbase + it] = stat;
         if (a.gi_iters) a.gi_iters[sbase + it] = it_iter;
         it_iter = 0;
