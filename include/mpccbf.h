@@ -246,7 +246,9 @@ int mpccbf_cbf_rows(mpccbf_handle* h, int32_t num_scenarios, const double* state
  *                         falls back to zero control: CBFFormationControl_example.cpp:168-172)
  *   status    [S][N]      SolveStatus;  lambda2 [S] algebraic connectivity (may be NULL)
  * One warp per scenario: num_agents <= 32, else MPCCBF_ERR_UNSUPPORTED. Uses cfg d_min, d_max,
- * cbf_gamma, v_min, v_max, feas_tol. Device pointers, async on `cuda_stream`. */
+ * cbf_gamma, v_min, v_max, feas_tol, and slack_mode / slack_cost / slack_decay: in slack mode
+ * (ConnectivityControl.cpp:30-45) slack i (cost slack_cost * slack_decay^i) relaxes safety row i and CLF row i,
+ * the last slack the connectivity row; the velocity rows stay hard. Device pointers, async on `cuda_stream`. */
 int mpccbf_cbf_filter_batch(mpccbf_handle* h, int32_t num_scenarios, const double* states,
                             const double* desired_u, double* u, int32_t* status, double* lambda2,
                             void* cuda_stream);

@@ -95,6 +95,107 @@ struct FilterRows {
     __device__ __forceinline__ void normal(int id, double (&np)[2], double& rhs) const { row(id, np, rhs); }
 };
 
+// Slack mode (ConnectivityControl.cpp:30-45, CBFQPGeneratorBase.cpp:9-30,59-70): N slacks s_g >= 0 with linear cost
+// w_g = slack_cost * slack_decay^g; safety row g and CLF row g share s_g (g < N - 1), the connectivity row has s_{N-1};
+// the velocity rows stay hard. With the slacks eliminated this is the capped-multiplier problem of gi_solver.h:
+// group g = {safety row, CLF row, "none"} (or {connectivity row, "none"}), one piece of it the leader.
+// Row ids: 0..3 the velocity rows (hard), 4 + 3 g + p with p = 0 safety / connectivity, 1 CLF, 2 "none".
+struct FilterRowsSoft {
+    FilterRows r;
+    unsigned char* lead;  // [N] leaders of this agent's groups: 0 none, 1 + p
+    double slack_cost, slack_decay;
+
+    // piece p < 2 of group g as a row np.u >= rhs; false when the group has no such piece
+    __device__ __forceinline__ bool piece(int g, int p, double (&np)[2], double& rhs) const {
+        const int N = r.N;
+        if (g == N - 1) {
+            if (p != 0 || !r.use_conn) return false;
+            r.row(N + 3, np, rhs);
+            return true;
+        }
+        if (p == 0) {
+            r.row(g, np, rhs);
+            return true;
+        }
+        if (r.use_conn) return false;
+        r.row(N + 3 + g, np, rhs);
+        return true;
+    }
+    __device__ __forceinline__ void check_hard(int id, const double (&v)[2], double& best, int& best_id) const {
+        double np[2], rhs;
+        r.row(r.N - 1 + id, np, rhs);
+        const double viol = rhs - fma(np[0], v[0], np[1] * v[1]);
+        if (viol > r.tol * fmax(1.0, fabs(rhs)) && rhs > -1e20) {
+            const double score = viol;  // unit normals
+            if (score > best) {
+                best = score;
+                best_id = id;
+            }
+        }
+    }
+    __device__ __forceinline__ void scan(const double (&v)[2], double& best, int& best_id) const {
+        for (int id = 0; id < 4; ++id) check_hard(id, v, best, best_id);
+        for (int g = 0; g < r.N; ++g) {
+            const int ld = lead[g];
+            double nl[2] = {0.0, 0.0}, rl = 0.0, gl = 0.0;
+            if (ld) {
+                piece(g, ld - 1, nl, rl);
+                gl = rl - fma(nl[0], v[0], nl[1] * v[1]);
+            }
+            for (int p = 0; p < 2; ++p) {
+                double np[2], rhs;
+                if (!piece(g, p, np, rhs)) continue;
+                if (!(rhs > -1e20)) continue;   // upper bound >= 1e20 in the reference's orientation: no row
+                const double gp = rhs - fma(np[0], v[0], np[1] * v[1]);
+                double viol, thr = r.tol * fmax(1.0, fabs(rhs)), nn;
+                int id = 4 + 3 * g + p;
+                if (ld == 0 || ld == p + 1) {
+                    viol = ld ? -gp : gp;   // the leader itself: piece "none" is violated once the row holds again
+                    if (ld) id = 4 + 3 * g + 2;
+                    nn = fma(np[0], np[0], np[1] * np[1]);
+                } else {
+                    viol = gp - gl;
+                    thr = r.tol * fmax(fmax(1.0, fabs(rhs)), fabs(rl));
+                    const double d0 = np[0] - nl[0], d1 = np[1] - nl[1];
+                    nn = fma(d0, d0, d1 * d1);
+                }
+                if (viol > thr) {
+                    const double score = (nn > 0.0) ? viol * rsqrt(nn) : 1e150;  // independent of u: taken up by the slack
+                    if (score > best) {
+                        best = score;
+                        best_id = id;
+                    }
+                }
+            }
+        }
+    }
+    __device__ __forceinline__ void normal(int id, double (&np)[2], double& rhs) const {
+        if (id < 4) {
+            r.row(r.N - 1 + id, np, rhs);
+            return;
+        }
+        const int g = (id - 4) / 3, p = (id - 4) - 3 * g;
+        np[0] = np[1] = 0.0;
+        rhs = 0.0;
+        if (p < 2) piece(g, p, np, rhs);
+        const int ld = lead[g];
+        if (ld) {
+            double nl[2], rl;
+            piece(g, ld - 1, nl, rl);
+            np[0] -= nl[0];
+            np[1] -= nl[1];
+            rhs -= rl;
+        }
+    }
+    __device__ __forceinline__ int group(int id) const { return id < 4 ? -1 : (id - 4) / 3; }
+    // the reference's cost is |u - u_d|^2 + sum w s (no 1/2): against 1/2 |u - u_d|^2 the weights are halved
+    __device__ __forceinline__ double weight(int g) const { return 0.5 * slack_cost * pow(slack_decay, static_cast<double>(g)); }
+    __device__ __forceinline__ void set_leader(int g, int id) const {
+        const int p = (id - 4) - 3 * g;
+        lead[g] = static_cast<unsigned char>(p < 2 ? p + 1 : 0);
+    }
+};
+
 struct FilterArgs {
     const double* states;     // [S][N][6]
     const double* desired_u;  // [S][N][3]   (may be NULL when only rows are wanted)
@@ -107,6 +208,8 @@ struct FilterArgs {
     double dmin2, dmax, gamma, tol;
     double vmin[3], vmax[3];
     int max_gi;
+    int slack;                // slack_mode
+    double slack_cost, slack_decay;
 };
 
 __global__ void __launch_bounds__(128) cbf_filter_kernel(const FilterArgs a) {
@@ -269,7 +372,22 @@ __global__ void __launch_bounds__(128) cbf_filter_kernel(const FilterArgs a) {
                 const double v0[2] = {__ldg(du), __ldg(du + 1)};
                 gi_init<2>(gi, v0);
                 int iters = 0;
-                int stat = gi_run<2>(gi, rows, a.max_gi, iters);
+                int stat;
+                if (a.slack) {
+                    // leaders of this agent's groups: N bytes in the eigenvector matrix's storage (free after fv was taken)
+                    FilterRowsSoft soft;
+                    soft.r = rows;
+                    soft.lead = reinterpret_cast<unsigned char*>(Vm) + self * 32;
+                    soft.slack_cost = a.slack_cost;
+                    soft.slack_decay = a.slack_decay;
+                    for (int gq = 0; gq < N; ++gq) soft.lead[gq] = 0;
+                    GISoft<2> gs;
+                    gs.grp[0] = gs.grp[1] = -1;
+                    gs.cap[0] = gs.cap[1] = HUGE_VAL;
+                    stat = gi_run<2, true, FilterRowsSoft>(gi, gs, soft, a.max_gi, iters, gi_vmax2<2>(v0));
+                } else {
+                    stat = gi_run<2>(gi, rows, a.max_gi, iters);
+                }
                 // yaw: -(w - wmin) <= u <= wmax - w
                 const double ylo = -(e[5] - a.vmin[2]), yhi = a.vmax[2] - e[5];
                 if (ylo > yhi + a.tol * fmax(1.0, fabs(yhi))) stat = (stat == MPCCBF_STATUS_OPTIMAL) ? MPCCBF_STATUS_INFEASIBLE : stat;
@@ -301,6 +419,9 @@ int launch_cbf_filter(const mpccbf_config& cfg, int S, const double* states, con
     a.tol = cfg.feas_tol > 0 ? cfg.feas_tol : 1e-9;
     for (int d = 0; d < 3; ++d) { a.vmin[d] = cfg.v_min[d]; a.vmax[d] = cfg.v_max[d]; }
     a.max_gi = 50 * (2 * N + 4) + 100;
+    a.slack = cfg.slack_mode ? 1 : 0;
+    a.slack_cost = cfg.slack_cost;
+    a.slack_decay = cfg.slack_decay;
     const int threads = 128;
     const size_t per_warp = sizeof(double) * (N * 6 + 2 * N * a.NP + N);
     const size_t smem = per_warp * (threads / 32);

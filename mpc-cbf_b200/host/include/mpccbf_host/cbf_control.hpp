@@ -5,8 +5,9 @@
 //        cbf/include/cbf/controller/ConnectivityControl.h:16-60, src/controller/ConnectivityControl.cpp:22-99
 // What differs, on purpose: ConnectivityCBF here is a parameter holder (the barrier expressions are
 // closed forms inside the kernel, gamma = 5 and lambda2_min = 0.1 as hard-coded in the reference,
-// ConnectivityCBF.cpp:62-63); slack_mode = true is not implemented by the device path and throws at
-// construction; on a failed solve cbf_u is zero (what the reference's driver substitutes,
+// ConnectivityCBF.cpp:62-63); slack_mode = true runs the same kernel with capped multipliers (the slack of neighbour i
+// shared by its safety and CLF rows, the last slack on the connectivity row, ConnectivityControl.cpp:30-45);
+// on a failed solve cbf_u is zero (what the reference's driver substitutes,
 // CBFFormationControl_example.cpp:168-172). BatchedConnectivityControl filters every agent of many
 // scenarios in one launch.
 #pragma once
@@ -58,11 +59,11 @@ class ConnectivityControl {
     ConnectivityControl(std::shared_ptr<ConnectivityCBF> cbf, int num_robots, bool slack_mode = false, T slack_cost = T(0),
                         T slack_decay_rate = T(0), int device = 0)
         : cbf_(std::move(cbf)), num_robots_(num_robots) {
-        (void)slack_cost;
-        (void)slack_decay_rate;
         if (!cbf_) throw std::invalid_argument("ConnectivityControl: cbf is null");
-        if (slack_mode) throw std::runtime_error("ConnectivityControl: slack_mode is not implemented by the device path");
         cfg_ = detail::filter_config(*cbf_, num_robots, 1, device);
+        cfg_.slack_mode = slack_mode ? 1 : 0;
+        cfg_.slack_cost = slack_cost;
+        cfg_.slack_decay = slack_decay_rate;
         mpc_cbf::detail::check(mpccbf_create(&cfg_, &h_), "ConnectivityControl");
     }
     ConnectivityControl(const ConnectivityControl&) = delete;
@@ -119,8 +120,12 @@ class BatchedConnectivityControl {
         std::vector<int32_t> status;   // [S][N]
         std::vector<double> lambda2;   // [S]
     };
-    BatchedConnectivityControl(const ConnectivityCBF& cbf, int num_robots, int max_scenarios, int device = 0)
+    BatchedConnectivityControl(const ConnectivityCBF& cbf, int num_robots, int max_scenarios, int device = 0,
+                               bool slack_mode = false, double slack_cost = 0.0, double slack_decay_rate = 0.0)
         : cfg_(detail::filter_config(cbf, num_robots, max_scenarios, device)) {
+        cfg_.slack_mode = slack_mode ? 1 : 0;
+        cfg_.slack_cost = slack_cost;
+        cfg_.slack_decay = slack_decay_rate;
         mpc_cbf::detail::check(mpccbf_create(&cfg_, &h_), "BatchedConnectivityControl");
     }
     BatchedConnectivityControl(const BatchedConnectivityControl&) = delete;

@@ -247,7 +247,15 @@ static void test_cbf_filter_on_device() {
     EXPECT_NEAR(u(1), 3.4635324630258153 / 2.70339242, 1e-6);
     EXPECT_NEAR(u(0), 0.0, 1e-12);
     EXPECT_THROW(ctl.optimize(u, {0.0, 0.0, 0.0}, states, 3, nlim, lim), std::out_of_range);
-    EXPECT_THROW(Control(cb, 3, true, 1.0, 0.1), std::runtime_error);
+    {   // slack mode (ConnectivityControl.cpp:30-45): the connectivity row carries the LAST slack, weight
+        // slack_cost * decay^(N-1) = 0.01. min (u_y - 4)^2 + 0.01 s  s.t.  -2.70339 u_y + 3.46353 + s >= 0: the multiplier
+        // of the row stops at its cap, u_y = 4 - (0.01 / 2) * 2.70339
+        Control soft(cb, 3, true, 1.0, 0.1);
+        math::VectorDIM<double, DIM> us;
+        EXPECT(soft.optimize(us, {0.0, 4.0, 0.0}, states, 0, nlim, lim));
+        EXPECT_NEAR(us(1), 4.0 - 0.005 * 2.70339242, 1e-6);
+        EXPECT_NEAR(us(0), 0.0, 1e-12);
+    }
     // batched sibling gives the same answer for the same snapshot
     cbf::BatchedConnectivityControl<double, DIM> batch(*cb, 3, 2);
     std::vector<double> st(2 * 3 * 6, 0.0), du(2 * 3 * 3, 0.0);

@@ -91,3 +91,33 @@ def test_filter_unsupported_and_errors(M):
         h.cbf_filter_batch_host(np.zeros((1, 33, 6)), np.zeros((1, 33, 3)))
     assert e.value.code == M.ERR_UNSUPPORTED
     h.close()
+
+
+@pytest.mark.parametrize("N,S,spread,cost,decay", [(2, 64, 0.8, 1000.0, 0.2), (4, 128, 1.0, 1000.0, 0.2), (8, 128, 1.6, 1000.0, 0.2),
+                                                    (8, 128, 1.2, 10.0, 0.7), (16, 128, 2.2, 10.0, 0.8)])
+def test_filter_slack_mode_parity(M, O, N, S, spread, cost, decay):
+    # ConnectivityControl.cpp:30-45: slack s_i on safety row i and CLF row i (shared), the last slack on the connectivity
+    # row, linear cost slack_cost * slack_decay^i; velocity rows stay hard. Tight swarms: without slack many QPs are
+    # infeasible, with slack only the velocity rows can make one infeasible.
+    vlim = [1.0, 1.0, 1.0]
+    kw = dict(num_agents=N, d_min=0.5, d_max=3.0, v_min=[-v for v in vlim], v_max=vlim)
+    st, du = random_swarms(S, N, 11 * N + 1, spread)
+    if N > 2:
+        st[1, 1, :2] = st[1, 0, :2] + [0.3, 0.0]   # inside d_min
+    st[0, 0, 3] = 1.4                               # outside the velocity box (hard rows): still solvable by braking
+    h0 = M.Handle(M.default_config(max_scenarios=S, **kw))
+    hard = h0.cbf_filter_batch_host(st, du)
+    h0.close()
+    h = M.Handle(M.default_config(max_scenarios=S, slack_mode=1, slack_cost=cost, slack_decay=decay, **kw))
+    got = h.cbf_filter_batch_host(st, du)
+    h.close()
+    ref = O.cbf_filter_batch(O.base_config(slack_mode=1, slack_cost=cost, slack_decay=decay, **kw), st, du, prec=1)
+    clear = np.abs(ref["lambda2"] - 0.1) > 1e-8
+    assert np.array_equal(got["status"][clear], ref["status"][clear])
+    ok = (ref["status"] == 0) & clear[:, None]
+    assert ok.mean() > 0.9
+    err = np.abs(got["u"] - ref["u"])[ok].max()
+    assert err < 1e-5, err
+    # slack did something: QPs that are infeasible with hard rows are solved, and solved ones can differ
+    assert ((hard["status"] != 0) & (got["status"] == 0)).any() or N == 2
+    print(f"filter slack N={N}: max |u - oracle| {err:.2e}, hard infeasible {np.mean(hard['status'] != 0):.2f} -> slack infeasible {np.mean(got['status'] != 0):.3f}")
