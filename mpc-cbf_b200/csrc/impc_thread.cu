@@ -598,23 +598,50 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     }
     const float kinv = static_cast<float>(c.scn[3]);  // (K - 1) / t_{K-1}
     int total_iter = 0;
-    // ---- yaw: 2-dof projection, shared by every IMPC iteration --------------------------------
+    // ---- bound rows only: the axes decouple, so yaw (final) and the stage-A solution of x / y are three 2-dof
+    // projections through ONE rolled loop (a 2-dof step and scan cost about a third of the coupled 4-dof ones; the coupled
+    // state is assembled from the two axis solutions: same minimiser, the problem is separable) -------------------------
     typename GICore<2, CORE>::State gy;
-    GICore<2, CORE>::init(gy, v0 + 4);
-    int base_status;
+    int base_status = MPCCBF_STATUS_OPTIMAL;
+    double axv[3][2], axu[2][2];
+    int axid[2][2], axq[2] = {0, 0};
+    constexpr bool kAxisStageA = (CORE == 0);
     {
         RowsAxis ry;
         ry.tm = c.tm;
         ry.K = K;
-        ry.s0 = s[2][0];
-        ry.s1 = s[2][1];
         ry.tol = T.feas_tol;
         ry.pq = c.pq;
         ry.scn = c.scn;
         ry.kinv = kinv;
-        ry.lim = c.lim + 16;
         GISoft<2> gsy;
-        base_status = GICore<2, CORE>::template run<false>(gy, gsy, ry, T.max_gi, total_iter, gi_vmax2<2>(v0 + 4));
+#pragma unroll 1
+        for (int axi = (kAxisStageA ? 0 : 2); axi < 3; ++axi) {
+            // yaw first would let an infeasible yaw skip x / y; the order only matters for which status is reported
+            const int ax = (axi == 0) ? 2 : axi - 1;
+            if (base_status != MPCCBF_STATUS_OPTIMAL) break;
+            const double va = (ax == 0) ? v0[0] : ((ax == 1) ? v0[2] : v0[4]);
+            const double vb = (ax == 0) ? v0[1] : ((ax == 1) ? v0[3] : v0[5]);
+            const double vv[2] = {va, vb};
+            ry.s0 = (ax == 0) ? s[0][0] : ((ax == 1) ? s[1][0] : s[2][0]);
+            ry.s1 = (ax == 0) ? s[0][1] : ((ax == 1) ? s[1][1] : s[2][1]);
+            ry.lim = c.lim + 8 * ax;
+            GICore<2, CORE>::init(gy, vv);
+            base_status = GICore<2, CORE>::template run<false>(gy, gsy, ry, T.max_gi, total_iter, gi_vmax2<2>(vv));
+            if constexpr (kAxisStageA) {
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    if (ax == 0) { axv[0][i] = gy.v[i]; axu[0][i] = gy.u[i]; axid[0][i] = gy.id[i]; }
+                    if (ax == 1) { axv[1][i] = gy.v[i]; axu[1][i] = gy.u[i]; axid[1][i] = gy.id[i]; }
+                    if (ax == 2) axv[2][i] = gy.v[i];
+                }
+                if (ax == 0) axq[0] = gy.q;
+                if (ax == 1) axq[1] = gy.q;
+            } else {
+                axv[2][0] = gy.v[0];
+                axv[2][1] = gy.v[1];
+            }
+        }
     }
     // ---- x/y stage A: bound rows only ---------------------------------------------------------
     RowsXY<SOFT, CONN> rx;
@@ -656,6 +683,29 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         gs.cap[i] = HUGE_VAL;
     }
     GICore<4, CORE>::init(gx, v0);
+    if constexpr (kAxisStageA) {
+        // coupled stage-A state from the two axis solutions: iterate, then the active rows of x followed by those of y
+        // (axis row id (dsel K + k) << 1 | side  ->  ((dsel K + k) 2 + axis) << 1 | side)
+        if (base_status == MPCCBF_STATUS_OPTIMAL) {
+            gx.v[0] = axv[0][0]; gx.v[1] = axv[0][1]; gx.v[2] = axv[1][0]; gx.v[3] = axv[1][1];
+            int q = 0;
+#pragma unroll
+            for (int ax = 0; ax < 2; ++ax)
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+                    if (i < axq[ax]) {
+                        const int id = ((((axid[ax][i] >> 1) << 1) + ax) << 1) | (axid[ax][i] & 1);
+#pragma unroll
+                        for (int col = 0; col < 4; ++col)
+                            if (col == q) {
+                                gx.u[col] = axu[ax][i];
+                                gx.id[col] = id;
+                            }
+                        ++q;
+                    }
+            gx.q = q;
+        }
+    }
     // stage-A solution: iterate, multipliers and ids of its active bound rows (the factorisation is
     // rebuilt from the ids when a later IMPC iteration has to start from it again)
 
@@ -673,11 +723,23 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     // only such rows, its (v, multipliers, active set) is a solution pair of a SUB-problem of the next iteration — a
     // valid starting point of the dual method — so the next iteration continues from it instead of from stage A and
     // only adds what its new rows (k >= 1, rebuilt at the new predicted states) require. Same minimiser (it is
-    // unique); measured on the bench workload: 4.9 -> ~1 active-set steps in iteration 1.
+    // unique); measured on the bench workload: 4.9 -> 4.0 active-set steps in iteration 1 (its k = 1 rows displace most of
+    // what iteration 0 found).
     bool reuse = false;
     double pen_last = 0.0;  // slack mode: sum_j w_j s_j of the last successful iterate
     const size_t sbase = static_cast<size_t>(g) * T.iters;
     int mode = kStageA, it = 0, it_iter = 0;
+    if constexpr (kAxisStageA) {   // stage A is done: its solution is the snapshot every iteration can restart from
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            c.snapd[i * kLS] = gx.v[i];
+            c.snapd[(4 + i) * kLS] = gx.u[i];
+            c.snapi[i * kLSI] = gx.id[i];
+        }
+        c.snapi[4 * kLSI] = gx.q;
+        it_iter = total_iter;
+        mode = kIter;
+    }
     while (it < T.iters) {
         int stat = base_status;
         bool run = false;
@@ -799,8 +861,8 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         ++n_ok;
 #pragma unroll
         for (int i = 0; i < 4; ++i) c.sol[i * kLS] = gx.v[i];
-        c.sol[4 * kLS] = gy.v[0];
-        c.sol[5 * kLS] = gy.v[1];
+        c.sol[4 * kLS] = axv[2][0];
+        c.sol[5 * kLS] = axv[2][1];
         if constexpr (SOFT) pen_last = (run && a.objective) ? rx.penalty(gx.v) : 0.0;
         if (a.ctrl_all) {  // every iterate (mpccbf_optimize_one): small batches, direct stores
             double* out = a.ctrl_all + (sbase + it) * T.n;

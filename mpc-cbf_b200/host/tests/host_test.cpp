@@ -248,12 +248,12 @@ static void test_cbf_filter_on_device() {
     EXPECT_NEAR(u(0), 0.0, 1e-12);
     EXPECT_THROW(ctl.optimize(u, {0.0, 0.0, 0.0}, states, 3, nlim, lim), std::out_of_range);
     {   // slack mode (ConnectivityControl.cpp:30-45): the connectivity row carries the LAST slack, weight
-        // slack_cost * decay^(N-1) = 0.01. min (u_y - 4)^2 + 0.01 s  s.t.  -2.70339 u_y + 3.46353 + s >= 0: the multiplier
-        // of the row stops at its cap, u_y = 4 - (0.01 / 2) * 2.70339
+        // slack_cost * decay^(N-1) = 0.01. min (u_y - 2.5)^2 + 0.01 s  s.t.  -2.70339 u_y + 3.46353 + s >= 0: the multiplier
+        // of the row stops at its cap, u_y = 2.5 - (0.01 / 2) * 2.70339 (the hard rows would cap u_y at 1.2812)
         Control soft(cb, 3, true, 1.0, 0.1);
         math::VectorDIM<double, DIM> us;
-        EXPECT(soft.optimize(us, {0.0, 4.0, 0.0}, states, 0, nlim, lim));
-        EXPECT_NEAR(us(1), 4.0 - 0.005 * 2.70339242, 1e-6);
+        EXPECT(soft.optimize(us, {0.0, 2.5, 0.0}, states, 0, nlim, lim));
+        EXPECT_NEAR(us(1), 2.5 - 0.005 * 2.70339242, 1e-6);
         EXPECT_NEAR(us(0), 0.0, 1e-12);
     }
     // batched sibling gives the same answer for the same snapshot
