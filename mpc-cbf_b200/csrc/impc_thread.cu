@@ -993,11 +993,10 @@ static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count) {
 }
 
 // Launch shapes (threads per CTA, CTAs per SM the register budget is set for). All keep >= 14 warps per SM, which is what
-// one wave of the 4096 x 16 workload needs on 148 SMs:  0: 128 x 4 (128 registers / thread)   1: 448 x 1 (146; the constant
-// tables are staged once per SM)   2: 224 x 2 (146)
+// one wave of the 4096 x 16 workload needs on 148 SMs:  0: 128 x 4 (128 registers / thread, the measured best and the
+// default)   2: 224 x 2 (144)   3: 64 x 7 (144). Shape 1 (448 x 1) was dropped: its launch exceeds the register file.
 template <int CFG> struct ThreadCfg;
 template <> struct ThreadCfg<0> { static constexpr int kThreads = 128, kCtas = 4; };
-template <> struct ThreadCfg<1> { static constexpr int kThreads = 448, kCtas = 1; };
 template <> struct ThreadCfg<2> { static constexpr int kThreads = 224, kCtas = 2; };
 template <> struct ThreadCfg<3> { static constexpr int kThreads = 64, kCtas = 7; };
 
@@ -1207,13 +1206,10 @@ int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cuda
     // Active-set core and launch shape: measured defaults (profiles/r2*_variants.md); MPCCBF_THREAD_CORE = 0 / 1 and
     // MPCCBF_THREAD_CFG = 0 / 1 / 2 override them for experiments.
     static const int core = [] { const char* e = std::getenv("MPCCBF_THREAD_CORE"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CORE; return v == 1 ? 1 : 0; }();
-    static const int cfgi = [] { const char* e = std::getenv("MPCCBF_THREAD_CFG"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CFG; return (v >= 1 && v <= 3) ? v : 0; }();
+    static const int cfgi = [] { const char* e = std::getenv("MPCCBF_THREAD_CFG"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CFG; return (v == 2 || v == 3) ? v : 0; }();
     ThreadKernel kern;
     int threads;
-    if (cfgi == 1) {
-        kern = core ? pick_kernel<1, 1>(T) : pick_kernel<0, 1>(T);
-        threads = ThreadCfg<1>::kThreads;
-    } else if (cfgi == 2) {
+    if (cfgi == 2) {
         kern = core ? pick_kernel<1, 2>(T) : pick_kernel<0, 2>(T);
         threads = ThreadCfg<2>::kThreads;
     } else if (cfgi == 3) {
