@@ -965,12 +965,14 @@ struct ThreadSmemLayout {
     // per warp (bytes from the warp's block): the fixed-offset arrays (kOffSol .. kOffPred), then
     int off_conn, off_fied, off_st;  // conn_mode rows and Fiedler vectors (empty otherwise), scenario states
     int n_fied;
+    int apw;                         // agents per warp (a tile): 32, or fewer so that a small batch still fills the SMs
     int nscen_max;
     int shared_bytes, warp_bytes;
 };
 
-static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count) {
+static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count, int apw) {
     ThreadSmemLayout L;
+    L.apw = apw;
     L.n_tm = 3 * T.K * kTmplStride;
     L.n_vr = 2 * T.K;
     L.n_yw = T.m1 * 4;
@@ -982,7 +984,7 @@ static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count) {
     L.shared_bytes = (8 * L.off_omap + T.n * 2 + 15) / 16 * 16;
     // scenarios a tile of 32 consecutive agents can touch
     const int ac = std::max(agent_count, 1);
-    L.nscen_max = (32 % ac == 0) ? 32 / ac : (ac % 32 == 0 ? 1 : (32 - 1) / ac + 2);
+    L.nscen_max = (apw % ac == 0) ? apw / ac : (ac % apw == 0 ? 1 : (apw - 1) / ac + 2);
     const int H = std::max(T.H, 1);
     L.off_conn = kOffPred + H * 4 * kRow;
     L.off_fied = L.off_conn + (T.conn_mode ? H * 3 * kRow : 0);
@@ -1050,12 +1052,13 @@ __device__ __forceinline__ void thread_kernel_body(const DevTables& T, const Ste
     const int warps_per_cta = blockDim.x >> 5;
     const int gwarp = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
     const int total_warps = gridDim.x * warps_per_cta;
-    const int ntiles = (a.num_qp + 31) >> 5;
+    const int apw = L.apw;
+    const int ntiles = (a.num_qp + apw - 1) / apw;
     const int N = T.N, n = T.n;
 
     for (int tile = gwarp; tile < ntiles; tile += total_warps) {
-        const int g0 = tile << 5;
-        const int cnt = min(32, a.num_qp - g0);
+        const int g0 = tile * apw;
+        const int cnt = min(apw, a.num_qp - g0);
         const int s_lo = g0 / a.agent_count;
         const int s_hi = (g0 + cnt - 1) / a.agent_count;
         {   // stage the tile's scenarios (coalesced 16-byte loads)
@@ -1219,8 +1222,16 @@ int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cuda
         kern = core ? pick_kernel<1, 0>(T) : pick_kernel<0, 0>(T);
         threads = ThreadCfg<0>::kThreads;
     }
-    const ThreadSmemLayout L = thread_layout(T, a.agent_count);
-    const int ntiles = (a.num_qp + 31) / 32;
+    // Agents per warp. The kernel is latency-bound (its duration is that of its slowest warp, ~5 us per active-set step of
+    // one thread), and a warp executes the union of what its agents need. Measured (tools/apw_sweep.sh): fewer agents per
+    // warp only pay when every agent can have a warp of its own in one wave (2048 agents: 0.127 vs 0.145 ms); in
+    // between, 32 agents per warp win (more warps per SM cost more than shorter warps gain). One agent's arithmetic
+    // does not depend on it. MPCCBF_THREAD_APW overrides (experiments).
+    static const int apw_env = [] { const char* e = std::getenv("MPCCBF_THREAD_APW"); return e ? std::atoi(e) : 0; }();
+    int apw = (a.num_qp <= 16 * sm_count) ? 1 : 32;
+    if (apw_env >= 1 && apw_env <= 32 && (apw_env & (apw_env - 1)) == 0) apw = apw_env;
+    const ThreadSmemLayout L = thread_layout(T, a.agent_count, apw);
+    const int ntiles = (a.num_qp + apw - 1) / apw;
     // small batches: no more warps per CTA than there are tiles per SM (keeps the grid spread over the SMs)
     const int want = std::max(1, (ntiles + sm_count - 1) / std::max(1, sm_count));
     while (threads > 32 && threads / 32 > want && (threads / 32) % 2 == 0 && threads > 128) threads /= 2;

@@ -42,3 +42,11 @@ for step in range(41):
               f"(A {a.max(1).mean():.2f} i0 {i0.max(1).mean():.2f} i1 {i1.max(1).mean():.2f})  zero-step agents {np.mean(tot==0):.2f}  "
               f"status!=0 {np.mean(status.cpu().numpy()[:,:,0]!=0):.3f}", flush=True)
     h.rollout(S, cur, ctrl, ncv, cur)
+
+# tail of the distribution at the last snapshot: the kernel cannot finish before its slowest agent
+st_np = status.cpu().numpy().reshape(-1, 2)
+for name, sel in (("all", np.ones(len(tot), bool)), ("both iterations OPTIMAL", (st_np[:, 0] == 0) & (st_np[:, 1] == 0)), ("some iteration not OPTIMAL", (st_np[:, 0] != 0) | (st_np[:, 1] != 0))):
+    t = tot[sel]
+    if len(t):
+        print(f"steps per agent, {name} ({len(t)}): mean {t.mean():.2f} p50 {np.percentile(t,50):.0f} p90 {np.percentile(t,90):.0f} p99 {np.percentile(t,99):.0f} p99.9 {np.percentile(t,99.9):.0f} max {t.max():.0f}")
+print("it0 max", gi[:, 0].max(), "it1 max", gi[:, 1].max(), "stageA+yaw max", ga[:, 0].max())
