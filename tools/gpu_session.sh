@@ -34,6 +34,10 @@ ncu --set full --metrics smsp__sass_thread_inst_executed_op_dfma_pred_on.sum,sms
     --clock-control none --import-source on -k regex:impc_thread_kernel -s 30 -c 1 -f -o $O/${TAG}_fused \
     python bench.py --steps 2 --warmup 3 --no-extras --no-cpu-baseline --no-graph --device-only > $O/${TAG}_ncu_full.log 2>&1
 tail -2 $O/${TAG}_ncu_full.log
+echo "== ncu full, latency path (one 8-agent scenario: 32 lanes per agent)"
+ncu --set full --clock-control none --import-source on -k regex:impc_reduced_kernel -s 5 -c 1 -f -o $O/${TAG}_lanes \
+    python bench.py --scenarios 1 --agents 8 --steps 4 --warmup 3 --no-extras --no-cpu-baseline --no-graph --device-only > $O/${TAG}_ncu_lanes.log 2>&1
+tail -2 $O/${TAG}_ncu_lanes.log
 echo "== reference arm"; python bench.py --impl reference --steps 20 --warmup 5 > $O/${TAG}_bench_ref.json 2>> $O/${TAG}_bench.err; cut -c1-200 $O/${TAG}_bench_ref.json
 nvidia-smi --query-gpu=name,clocks.max.sm,clocks.sm --format=csv > $O/${TAG}_smi.csv
 echo "== done"
