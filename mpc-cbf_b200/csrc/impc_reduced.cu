@@ -22,6 +22,7 @@
 #include <string>
 #include <vector>
 
+#include "gi_solver.h"
 #include "kernels.h"
 
 namespace mpccbf {
@@ -237,25 +238,27 @@ __host__ __device__ int solve_projection(const QPData& qp, const double (&v0)[R]
 #pragma unroll
                 for (int k = i + 1; k < R; ++k)
                     if (k < q) sacc = fma(-Rm[i][k], rr[k], sacc);
-                rr[i] = (i < q) ? sacc / Rm[i][i] : 0.0;
+                rr[i] = (i < q) ? sacc * GI_RCP(Rm[i][i]) : 0.0;
             }
             const double zt = 1e4 * 2.220446049250313e-16;
             const bool z_zero = !(ztn > zt * zt * dall);
-            double t1 = kInf;
+            // ratio test by cross-multiplication (u_j >= 0, rr_j > 0); no called division routine in the step (gi_solver.h)
+            double t1 = kInf, un = 0.0, rd = 0.0;
             int lpos = -1;
 #pragma unroll
             for (int j = 0; j < R; ++j)
                 if (j < q && rr[j] > 0.0) {
-                    const double t = u[j] / rr[j];
-                    if (t < t1) {
-                        t1 = t;
+                    if (lpos < 0 || u[j] * rd < un * rr[j]) {
+                        un = u[j];
+                        rd = rr[j];
                         lpos = j;
                     }
                 }
+            if (lpos >= 0) t1 = un * GI_RCP(rd);
             double sp = -rhs;
 #pragma unroll
             for (int i = 0; i < R; ++i) sp = fma(np[i], v[i], sp);
-            const double t2 = z_zero ? kInf : (-sp / ztn);
+            const double t2 = z_zero ? kInf : (-sp * GI_RCP(ztn));
             const double t = fmin(t1, t2);
             if (!(t < kInf)) return MPCCBF_STATUS_INFEASIBLE;
             if (!z_zero) {
@@ -273,9 +276,10 @@ __host__ __device__ int solve_projection(const QPData& qp, const double (&v0)[R]
                 for (int k = R - 1; k >= 1; --k) {
                     if (k > q) {
                         const double a = d[k - 1], b = d[k];
-                        const double hh = sqrt(fma(a, a, b * b));
-                        if (hh > 0.0) {
-                            const double cs = a / hh, sn = b / hh;
+                        const double h2 = fma(a, a, b * b);
+                        if (h2 > 0.0) {
+                            const double ih = GI_RSQRT(h2), hh = h2 * ih;
+                            const double cs = a * ih, sn = b * ih;
                             d[k - 1] = hh;
                             d[k] = 0.0;
 #pragma unroll
@@ -316,9 +320,10 @@ __host__ __device__ int solve_projection(const QPData& qp, const double (&v0)[R]
             for (int k = 0; k < R - 1; ++k)
                 if (k >= lpos && k < q) {
                     const double a = Rm[k][k], b = Rm[k + 1][k];
-                    const double hh = sqrt(fma(a, a, b * b));
-                    if (hh > 0.0) {
-                        const double cs = a / hh, sn = b / hh;
+                    const double h2 = fma(a, a, b * b);
+                    if (h2 > 0.0) {
+                        const double ih = GI_RSQRT(h2);
+                        const double cs = a * ih, sn = b * ih;
 #pragma unroll
                         for (int col = 0; col < R; ++col)
                             if (col >= k) {
@@ -429,12 +434,12 @@ __host__ __device__ void impc_agent(const DevTables& T, const StepArgs& a, int g
             double ax, ay, b;
             safety_row(px, py, vx, vy, o[0], o[1], o[3], o[4], T.dmin2, T.gamma, ax, ay, b);
             const double* t = tm + (2 * K + k) * kTmplStride;
-            const double an = sqrt(ax * ax + ay * ay) * sqrt(t[0] * t[0] + t[1] * t[1]);
+            const double an2 = (ax * ax + ay * ay) * (t[0] * t[0] + t[1] * t[1]);
             double* c = rows + 4 * j;
             c[0] = ax;
             c[1] = ay;
             c[2] = b;
-            c[3] = (an > 0.0) ? 1.0 / an : kInf;
+            c[3] = (an2 > 0.0) ? GI_RSQRT(an2) : kInf;   // only ranks the violated rows (whitened distance)
         }
         Grp<W>::sync(gmask);
         qp.ncbf = ncbf;
