@@ -388,11 +388,12 @@ void fill_episode_consts(const mpccbf_handle* h, EpisodeArgs& a) {
 int resolve_lanes(const mpccbf_handle* h, int64_t num_qp, bool force_auto = false) {
     int lanes = force_auto ? -1 : h->lanes;
     if (lanes < 0) {
-        // Measured crossover on B200 (profiles/r1h_kernel_crossover.md): a warp per agent (32 lanes split
-        // the row scan) wins while all its warps fit in one wave of 8 per SM — twice that for dense swarms,
-        // where a scan walks hundreds of safety rows; the thread-per-agent kernel wins beyond. The 8-lane
-        // variant is only the large-batch fallback for configurations without the polynomial row structure.
-        const int wave = 8 * h->sm_count * (h->cfg.num_agents >= 128 ? 2 : 1);
+        // Measured crossover on B200 (profiles/r2_kernel_ab.md section 5; round 1: profiles/r1h_kernel_crossover.md): a warp
+        // per agent (32 lanes split the row scan; ~3.6 us per active-set step against ~5 us for one thread) wins while
+        // its warps fit in two waves of 8 per SM (2368 agents: 0.094 vs 0.127 ms at 2048 agents, a tie at 4096); the
+        // thread-per-agent kernel wins beyond. The 8-lane variant is only the large-batch fallback for configurations
+        // without the polynomial row structure.
+        const int wave = 16 * h->sm_count;
         lanes = (num_qp <= wave) ? 32 : 0;
     }
     if (h->cfg.slack_mode || h->cfg.conn_mode) lanes = 0;  // capped multipliers / lifted connectivity rows: thread-per-agent kernel only
