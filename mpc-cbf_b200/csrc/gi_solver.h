@@ -26,6 +26,7 @@
 // Replaces qpcpp::CPLEXSolver::solve (qpcpp/src/solvers/CPLEX.cpp:35-178) for the reduced QP.
 #pragma once
 #include <cmath>
+#include <type_traits>
 
 #include "../../include/mpccbf.h"
 
@@ -71,7 +72,17 @@ struct GIState {
     double v[D];      // current iterate
     int id[D];        // row ids of the active set
     int q;            // number of active rows
+    // Optional cache of the active rows' normals, used when the row provider declares kCacheNormals: nc[(c D + i) kNcStride]
+    // = component i of active row c (storage of the caller: a lane-strided shared-memory block in the fused kernel).
+    // It is rebuilt from the ids by gi_refresh whenever the state was set from (v, u, ids).
+    double* nc;
 };
+constexpr int kNcStride = 32;
+
+template <class R, class = void>
+struct gi_caches_normals : std::false_type {};
+template <class R>
+struct gi_caches_normals<R, std::void_t<decltype(R::kCacheNormals)>> : std::true_type {};
 
 // group bookkeeping of the active rows (SOFT rows only)
 template <int D>
@@ -108,6 +119,34 @@ MPCCBF_HD void gi_remove(GIState<D>& g, GISoft<D>& gs, int lpos) {
     g.id[D - 1] = -1;
     if constexpr (SOFT) gs.grp[D - 1] = -1;
     --g.q;
+}
+
+// normals of the active rows from their ids (providers that cache them)
+template <int D, class Rows>
+MPCCBF_HD void gi_refresh(GIState<D>& g, const Rows& rows) {
+    if constexpr (gi_caches_normals<Rows>::value) {
+#pragma unroll 1
+        for (int c = 0; c < g.q; ++c) {
+            int id = -1;
+#pragma unroll
+            for (int k = 0; k < D; ++k)
+                if (k == c) id = g.id[k];
+            double w[D], unused;
+            rows.normal(id, w, unused);
+#pragma unroll
+            for (int i = 0; i < D; ++i) g.nc[(c * D + i) * kNcStride] = w[i];
+        }
+    }
+}
+// the cache follows gi_remove: columns above lpos move down (g.q is already the new count)
+template <int D>
+MPCCBF_HD void gi_nc_shift(GIState<D>& g, int lpos) {
+#pragma unroll
+    for (int c = 0; c < D - 1; ++c)
+        if (c >= lpos && c < g.q) {
+#pragma unroll
+            for (int i = 0; i < D; ++i) g.nc[(c * D + i) * kNcStride] = g.nc[((c + 1) * D + i) * kNcStride];
+        }
 }
 
 // Rows must provide:
@@ -157,8 +196,14 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
             for (int c = 0; c < D; ++c) {
                 d1[c] = 0.0;
                 if (c < g.q) {
-                    double w[D], unused;
-                    rows.normal(g.id[c], w, unused);
+                    double w[D];
+                    if constexpr (gi_caches_normals<Rows>::value) {
+#pragma unroll
+                        for (int i = 0; i < D; ++i) w[i] = g.nc[(c * D + i) * kNcStride];
+                    } else {
+                        double unused;
+                        rows.normal(g.id[c], w, unused);
+                    }
 #pragma unroll
                     for (int p = 0; p < c; ++p) {
                         double s = 0.0;
@@ -277,6 +322,10 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
                     if (col == g.q) {
                         g.u[col] = up_mult;
                         g.id[col] = best_id;
+                        if constexpr (gi_caches_normals<Rows>::value) {
+#pragma unroll
+                            for (int i = 0; i < D; ++i) g.nc[(col * D + i) * kNcStride] = np[i];
+                        }
                         if constexpr (SOFT) {
                             gs.grp[col] = pgrp;
                             gs.cap[col] = pcap;
@@ -306,6 +355,7 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
                     if (c == a) aid = g.id[c];
                 rows.set_leader(g3, aid);
                 gi_remove<D, true>(g, gs, a);   // its multiplier is implicit from now on
+                gi_refresh<D>(g, rows);         // the group's other active rows are expressed against the new leader
                 // (the group's other active rows and, if it belongs to g3, the entering row are expressed against
                 // the new leader from here on: normal() reads the leader)
                 if (pgrp == g3) rows.normal(best_id, np, rhs);
@@ -313,6 +363,7 @@ __host__ __device__ int gi_run(GIState<D>& g, GISoft<D>& gs, const Rows& rows, i
             }
             // partial (or dual-only) step: active row lpos leaves
             gi_remove<D, SOFT>(g, gs, lpos);
+            if constexpr (gi_caches_normals<Rows>::value) gi_nc_shift<D>(g, lpos);
         }
     }
 }
@@ -665,7 +716,7 @@ struct GICore<D, 0> {
         return gi_run<D, SOFT, Rows>(g, gs, rows, max_iter, n_iter, vmax2);
     }
     template <class Rows>
-    MPCCBF_HD static void refactor(State&, const Rows&) {}
+    MPCCBF_HD static void refactor(State& g, const Rows& rows) { gi_refresh<D>(g, rows); }
 };
 template <int D>
 struct GICore<D, 1> {

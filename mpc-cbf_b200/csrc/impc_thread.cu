@@ -34,20 +34,20 @@ namespace mpccbf {
 #define MPCCBF_THREAD_CFG 0
 #endif
 #ifndef MPCCBF_CAND_MAX
-#define MPCCBF_CAND_MAX 32
+#define MPCCBF_CAND_MAX 16
 #endif
 constexpr int kCandMax = MPCCBF_CAND_MAX;   // candidate safety rows kept per agent (more: scan all rows)
 constexpr int kSolStride = 7;  // per-agent result record: v[6] (whitened free dof of the last successful iterate), n_ok
-constexpr int kSnapD = 8, kSnapI = 5;  // stage-A snapshot per agent: v[4], u[4] | id[4], q
-// Per-agent scratch is LANE-STRIDED: element i of an array belongs to lane l at [i * kLS + l] (doubles; the snapshot's ints
-// sit in 8-byte slots, kLSI ints apart), and the arrays of a warp follow each other at compile-time offsets, so every
-// access is one per-thread base plus an immediate (the tests' host build uses the same layout with lane 0).
-constexpr int kLS = 32, kLSI = 64;
+constexpr int kNcRows = 16;    // normals of the <= 4 active rows of the x / y problem (gi_solver.h: GIState::nc)
+// Per-agent scratch is LANE-STRIDED: element i of an array belongs to lane l at [i * kLS + l] (doubles), and the arrays
+// of a warp follow each other at compile-time offsets, so every access is one per-thread base plus an immediate (the
+// tests' host build uses the same layout with lane 0).
+constexpr int kLS = 32;
+static_assert(kLS == kNcStride, "the normal cache of gi_solver.h is lane-strided like the rest");
 constexpr int kRow = kLS * 8;                          // bytes of one lane-strided row
 constexpr int kOffSol = 0;
-constexpr int kOffSnapD = kOffSol + kSolStride * kRow;
-constexpr int kOffSnapI = kOffSnapD + kSnapD * kRow;
-constexpr int kOffCand = kOffSnapI + kSnapI * kRow;    // kCandMax rows of kLS unsigned shorts
+constexpr int kOffNc = kOffSol + kSolStride * kRow;
+constexpr int kOffCand = kOffNc + kNcRows * kRow;      // kCandMax rows of kLS unsigned shorts
 constexpr int kOffPred = kOffCand + kCandMax * kLS * 2;  // H * 4 rows; then (conn_mode) H * 3 rows, Fiedler vectors; scenario states
 // CTA-shared tables at compile-time offsets from the start of shared memory (doubles): pq[5][4], lim[3][8], scn[K][4];
 // the horizon-sized tables follow (ThreadSmemLayout)
@@ -326,6 +326,8 @@ struct RowsXY {
     int nnb;              // N - 1
     double slack_cost, slack_decay;
 
+    static constexpr bool kCacheNormals = true;   // gi_solver.h keeps the active rows' normals in GIState::nc
+
     MPCCBF_HD void cbf_row(int j, double& ax, double& ay, double& b, int& k) const {
         if constexpr (CONN) {
             if (j >= ncbf) {  // connectivity HOCBF row of horizon step j - ncbf (computed once per IMPC iteration)
@@ -522,8 +524,7 @@ struct AgentCtx {
     double* pred;                     // [(k*4 + c) * kLS]
     unsigned short* cand;             // [i * kLS]
     double* sol;                      // [kSolStride * kLS] result record of this agent
-    double* snapd;                    // [kSnapD * kLS] stage-A snapshot (doubles), snapi [kSnapI * kLSI] (ints)
-    int* snapi;
+    double* nc;                       // [kNcRows * kLS] normals of the active rows (GIState::nc)
     unsigned char* lead;              // [N-1] group leaders of this agent (slack mode), else NULL
     // conn_mode: algebraic connectivity and Fiedler vector of this agent's scenario, scratch for its connectivity rows
     double lam2;
@@ -682,6 +683,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
         gs.grp[i] = -1;
         gs.cap[i] = HUGE_VAL;
     }
+    if constexpr (CORE == 0) gx.nc = c.nc;
     GICore<4, CORE>::init(gx, v0);
     if constexpr (kAxisStageA) {
         // coupled stage-A state from the two axis solutions: iterate, then the active rows of x followed by those of y
@@ -704,6 +706,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                         ++q;
                     }
             gx.q = q;
+            GICore<4, CORE>::refactor(gx, rx);   // normals of the assembled active rows
         }
     }
     // stage-A solution: iterate, multipliers and ids of its active bound rows (the factorisation is
@@ -729,14 +732,18 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     double pen_last = 0.0;  // slack mode: sum_j w_j s_j of the last successful iterate
     const size_t sbase = static_cast<size_t>(g) * T.iters;
     int mode = kStageA, it = 0, it_iter = 0;
-    if constexpr (kAxisStageA) {   // stage A is done: its solution is the snapshot every iteration can restart from
+    // stage-A solution every iteration can restart from: 8 doubles + 5 ints that are written once and read at most once
+    // per IMPC iteration, so they may live wherever the compiler puts them (registers or its local-memory spill space)
+    double snv[4] = {0, 0, 0, 0}, snu[4] = {0, 0, 0, 0};
+    int snid[4] = {-1, -1, -1, -1}, snq = 0;
+    if constexpr (kAxisStageA) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            c.snapd[i * kLS] = gx.v[i];
-            c.snapd[(4 + i) * kLS] = gx.u[i];
-            c.snapi[i * kLSI] = gx.id[i];
+            snv[i] = gx.v[i];
+            snu[i] = gx.u[i];
+            snid[i] = gx.id[i];
         }
-        c.snapi[4 * kLSI] = gx.q;
+        snq = gx.q;
         it_iter = total_iter;
         mode = kIter;
     }
@@ -779,12 +786,12 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
                 } else if (dirty) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        gx.v[i] = c.snapd[i * kLS];
-                        gx.u[i] = c.snapd[(4 + i) * kLS];
-                        gx.id[i] = c.snapi[i * kLSI];
+                        gx.v[i] = snv[i];
+                        gx.u[i] = snu[i];
+                        gx.id[i] = snid[i];
                         if constexpr (SOFT) gs.grp[i] = -1;
                     }
-                    gx.q = c.snapi[4 * kLSI];
+                    gx.q = snq;
                     GICore<4, CORE>::refactor(gx, rx);
                 }
                 if (!reuse) dirty = false;
@@ -826,11 +833,11 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
             it_iter += total_iter;  // yaw iterations are booked on IMPC iteration 0
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                c.snapd[i * kLS] = gx.v[i];
-                c.snapd[(4 + i) * kLS] = gx.u[i];
-                c.snapi[i * kLSI] = gx.id[i];
+                snv[i] = gx.v[i];
+                snu[i] = gx.u[i];
+                snid[i] = gx.id[i];
             }
-            c.snapi[4 * kLSI] = gx.q;
+            snq = gx.q;
             mode = kIter;
             continue;
         }
@@ -1082,8 +1089,7 @@ __device__ __forceinline__ void thread_kernel_body(const DevTables& T, const Ste
             c.st = wst + (scen - s_lo) * N * 6;
             unsigned char* tb = wbase + lane * 8;   // every lane-strided array of this agent: tb + immediate
             c.sol = reinterpret_cast<double*>(tb + kOffSol);
-            c.snapd = reinterpret_cast<double*>(tb + kOffSnapD);
-            c.snapi = reinterpret_cast<int*>(tb + kOffSnapI);
+            c.nc = reinterpret_cast<double*>(tb + kOffNc);
             c.cand = reinterpret_cast<unsigned short*>(wbase + kOffCand) + lane;
             c.pred = reinterpret_cast<double*>(tb + kOffPred);
             c.conn = reinterpret_cast<double*>(tb + L.off_conn);
@@ -1134,8 +1140,7 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
     const int H = std::max(T.H, 1);
     std::vector<double> pred(static_cast<size_t>(H) * 4 * kLS), sol(static_cast<size_t>(kSolStride) * kLS);
     std::vector<unsigned short> cand(static_cast<size_t>(kCandMax) * kLS);
-    std::vector<double> snapd(static_cast<size_t>(kSnapD) * kLS), connrows(static_cast<size_t>(H) * 3 * kLS);
-    std::vector<int> snapi(static_cast<size_t>(kSnapI) * kLSI);
+    std::vector<double> ncache(static_cast<size_t>(kNcRows) * kLS), connrows(static_cast<size_t>(H) * 3 * kLS);
     std::vector<double> lim(24), scn(static_cast<size_t>(4) * T.K);
     std::vector<unsigned char> lead(static_cast<size_t>(std::max(T.N, 1)));
     fill_scan_tables(T, T.tmpl, lim.data(), scn.data(), 0, 1);
@@ -1151,8 +1156,7 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
         c.pred = pred.data();
         c.cand = cand.data();
         c.sol = sol.data();
-        c.snapd = snapd.data();
-        c.snapi = snapi.data();
+        c.nc = ncache.data();
         c.lam2 = (T.conn_mode && a.lambda2) ? a.lambda2[scen] : 0.0;
         c.fied = (T.conn_mode && a.fiedler) ? a.fiedler + static_cast<size_t>(scen) * T.N : nullptr;
         c.conn = connrows.data();
