@@ -1249,6 +1249,11 @@ int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cuda
     if (e != cudaSuccess) return e;
     int per_sm = 1;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem);
+    {   // experiments: shared-memory carve-out in percent of 228 KB (MPCCBF_THREAD_CARVEOUT); default: the driver's choice,
+        // the smallest that fits — the L1 it leaves holds the kernel's local memory (profiles/r2_kernel_ab.md section 6)
+        static const int co = [] { const char* v = std::getenv("MPCCBF_THREAD_CARVEOUT"); return v ? std::atoi(v) : -1; }();
+        if (co >= 0) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+    }
     if (e != cudaSuccess) return e;
     if (per_sm < 1) per_sm = 1;
     const int need = (ntiles + threads / 32 - 1) / (threads / 32);
