@@ -31,7 +31,7 @@ namespace mpccbf {
 #define MPCCBF_THREAD_CORE 0
 #endif
 #ifndef MPCCBF_THREAD_CFG
-#define MPCCBF_THREAD_CFG 0
+#define MPCCBF_THREAD_CFG 4
 #endif
 #ifndef MPCCBF_CAND_MAX
 #define MPCCBF_CAND_MAX 16
@@ -1002,8 +1002,11 @@ static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count, int a
 }
 
 // Launch shapes (threads per CTA, CTAs per SM the register budget is set for). All keep >= 14 warps per SM, which is what
-// one wave of the 4096 x 16 workload needs on 148 SMs:  0: 128 x 4 (128 registers / thread, the measured best and the
-// default)   2: 224 x 2 (144)   3: 64 x 7 (144). Shape 1 (448 x 1) was dropped: its launch exceeds the register file.
+// one wave of the 4096 x 16 workload needs on 148 SMs:  0: 128 x 4 (128 registers / thread)   2: 224 x 2 (144)
+// 3: 64 x 7 (144)   4: 224 x 2 at 128 registers — the measured best and the default: two CTAs of 7 warps need 159 KB of
+// shared memory per SM instead of 193 KB, so the driver picks the 164 KB carve-out and the L1, which holds the kernel's
+// local memory, is 64 KB instead of 32 KB (0.185 against 0.205 ms; profiles/r2_kernel_ab.md section 6).
+// Shape 1 (448 x 1) was dropped: its launch exceeds the register file.
 template <int CFG> struct ThreadCfg;
 template <> struct ThreadCfg<0> { static constexpr int kThreads = 128, kCtas = 4; };
 template <> struct ThreadCfg<2> { static constexpr int kThreads = 224, kCtas = 2; };
@@ -1017,6 +1020,11 @@ __device__ __forceinline__ void thread_kernel_body(const DevTables& T, const Ste
 template <bool SOFT, bool CONN, int CORE, int CFG>
 __global__ void __launch_bounds__(128, 4)
 impc_thread_kernel(const __grid_constant__ DevTables T, const __grid_constant__ StepArgs a, const __grid_constant__ ThreadSmemLayout L) {
+    thread_kernel_body<SOFT, CONN, CORE>(T, a, L);
+}
+template <bool SOFT, bool CONN, int CORE, int CFG>
+__global__ void __launch_bounds__(224, 2)
+impc_thread_kernel_b224(const __grid_constant__ DevTables T, const __grid_constant__ StepArgs a, const __grid_constant__ ThreadSmemLayout L) {
     thread_kernel_body<SOFT, CONN, CORE>(T, a, L);
 }
 template <bool SOFT, bool CONN, int CORE, int CFG>
@@ -1211,9 +1219,9 @@ int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cuda
     if (T.slack && !a.lead_ws) return cudaErrorInvalidValue;
     if (T.conn_mode && (!a.lambda2 || !a.fiedler)) return cudaErrorInvalidValue;
     // Active-set core and launch shape: measured defaults (profiles/r2*_variants.md); MPCCBF_THREAD_CORE = 0 / 1 and
-    // MPCCBF_THREAD_CFG = 0 / 1 / 2 override them for experiments.
+    // MPCCBF_THREAD_CFG = 0 / 2 / 3 / 4 override them for experiments.
     static const int core = [] { const char* e = std::getenv("MPCCBF_THREAD_CORE"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CORE; return v == 1 ? 1 : 0; }();
-    static const int cfgi = [] { const char* e = std::getenv("MPCCBF_THREAD_CFG"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CFG; return (v == 2 || v == 3) ? v : 0; }();
+    static const int cfgi = [] { const char* e = std::getenv("MPCCBF_THREAD_CFG"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CFG; return (v >= 2 && v <= 4) ? v : 0; }();
     ThreadKernel kern;
     int threads;
     if (cfgi == 2) {
@@ -1222,6 +1230,9 @@ int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cuda
     } else if (cfgi == 3) {
         kern = core ? pick_kernel<1, 2>(T) : pick_kernel<0, 2>(T);
         threads = ThreadCfg<3>::kThreads;
+    } else if (cfgi == 4) {   // 224 x 2 at 128 registers: 159 KB of shared memory per SM, i.e. the 164 KB carve-out (L1 64 KB)
+        kern = T.slack ? impc_thread_kernel_b224<true, false, 0, 0> : (T.conn_mode ? impc_thread_kernel_b224<false, true, 0, 0> : impc_thread_kernel_b224<false, false, 0, 0>);
+        threads = 224;
     } else {
         kern = core ? pick_kernel<1, 0>(T) : pick_kernel<0, 0>(T);
         threads = ThreadCfg<0>::kThreads;
