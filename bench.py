@@ -49,6 +49,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the weak-scaling and sharded-cfg4 sub-records")
     ap.add_argument("--device-only", action="store_true", help="skip the end-to-end legs (kernel variant comparisons)")
+    ap.add_argument("--e2e-depth", type=int, default=3, help="batches in flight in the end-to-end leg (one handle each)")
     ap.add_argument("--no-graph", action="store_true", help="launch every timed step from Python instead of CUDA graphs")
     ap.add_argument("--seed", type=int, default=20261104)
     return ap.parse_args()
@@ -398,7 +399,7 @@ def step_latency(torch, leg, count):
 
 
 def time_e2e(torch, M, leg, args, barrier, max_over_ranks, compact):
-    """The host-pointer C-ABI calls on pinned HOST buffers, two batches in flight over two handles: every step's
+    """The host-pointer C-ABI calls on pinned HOST buffers, --e2e-depth batches in flight (one handle each): every step's
     inputs cross PCIe host -> device and its result device -> host inside the timed region."""
     S, N, n, iters, R = leg.S, leg.N, leg.n, leg.iters, leg.R
     hs = [b["states"].cpu().pin_memory() for b in leg.sets]
@@ -411,16 +412,17 @@ def time_e2e(torch, M, leg, args, barrier, max_over_ranks, compact):
              "n_curves": torch.zeros((S, N), dtype=torch.int32).pin_memory(),
              "objective": torch.zeros((S, N), dtype=torch.float64).pin_memory()}
         return o, {k: v.numpy() for k, v in o.items()}
-    keep0, o0 = outs()
-    keep1, o1 = outs()
+    D = max(2, args.e2e_depth)                       # batches in flight, one handle (stream + workspaces) each
+    keeps, oo = zip(*[outs() for _ in range(D)])
+    o0 = oo[0]
     hs_np, htg_np = [x.numpy() for x in hs], htg.numpy()
-    h2 = M.Handle(leg.cfg)
-    hh, oo = (leg.h, h2), (o0, o1)
+    extra = [M.Handle(leg.cfg) for _ in range(D - 1)]
+    hh = (leg.h,) + tuple(extra)
     call = (lambda hd, st, o: hd.step_batch_host_compact_async(st, htg_np, o)) if compact else \
            (lambda hd, st, o: hd.step_batch_host_async(st, htg_np, o))
-    for i in range(max(args.warmup, 4)):
-        call(hh[i & 1], hs_np[i % R], oo[i & 1])
-        hh[i & 1].synchronize()
+    for i in range(max(args.warmup, 2 * D)):
+        call(hh[i % D], hs_np[i % R], oo[i % D])
+        hh[i % D].synchronize()
     # the K-step loop is run twice (a single host-side hiccup of ~100 ms is several steps' worth at K = 20); the
     # better of the two repetitions is reported, both are listed, and so is the median step-to-step interval
     reps, gaps = [], []
@@ -429,15 +431,15 @@ def time_e2e(torch, M, leg, args, barrier, max_over_ranks, compact):
         t0 = time.perf_counter()
         last = t0
         for i in range(args.steps):
-            k = i & 1
-            if i >= 2:
-                hh[k].synchronize()          # batch i - 2 is complete, its output buffers are free again
+            k = i % D
+            if i >= D:
+                hh[k].synchronize()          # batch i - D is complete, its output buffers are free again
             call(hh[k], hs_np[(i + args.warmup) % R], oo[k])
             now = time.perf_counter()
             gaps.append(now - last)
             last = now
-        hh[0].synchronize()
-        hh[1].synchronize()
+        for hd in hh:
+            hd.synchronize()
         torch.cuda.synchronize()
         reps.append(max_over_ranks(time.perf_counter() - t0))
     secs = min(reps)
@@ -449,8 +451,9 @@ def time_e2e(torch, M, leg, args, barrier, max_over_ranks, compact):
         leg.h.synchronize()
     serial = max_over_ranks(time.perf_counter() - t0)
     barrier()
-    h2.close()
-    del keep0, keep1
+    for hd in extra:
+        hd.close()
+    del keeps
     h2d = S * N * (6 + 3) * 8
     d2h = S * N * ((6 if compact else n) * 8 + iters * 4 + 4 + 8)
     diag = {"repetitions_s": reps, "p50_step_interval_ms": 1e3 * float(np.median(gaps)), "max_step_interval_ms": 1e3 * float(np.max(gaps))}
@@ -632,12 +635,12 @@ def run_b200(args):
             "config": cfgd,
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d * world if world > 1 else h2d,
                     "d2h_bytes_per_step": d2h * world if world > 1 else d2h,
-                    "ms_per_step": 1e3 * e2e_s / args.steps, "pipeline_depth": 2, "result_form": "compact (v_free, 6 doubles per agent)",
+                    "ms_per_step": 1e3 * e2e_s / args.steps, "pipeline_depth": max(2, args.e2e_depth), "result_form": "compact (v_free, 6 doubles per agent)",
                     "serial_value": qps_total * args.steps / e2e_serial_s, "serial_ms_per_step": 1e3 * e2e_serial_s / args.steps,
                     "full_ctrl_pts_value": qps_total * args.steps / full_s, "full_ctrl_pts_d2h_bytes_per_step": d2h_full * world,
                     "full_ctrl_pts_serial_value": qps_total * args.steps / full_serial_s,
                     "timing": e2e_diag, "full_ctrl_pts_timing": full_diag,
-                    "note": "mpccbf_step_batch_host_compact_async on pinned host buffers, two batches in flight over two handles; "
+                    "note": "mpccbf_step_batch_host_compact_async on pinned host buffers, pipeline_depth batches in flight (one handle each); "
                             "bytes are summed over the ranks; serial_value = one blocking call per batch; full_ctrl_pts_* = the "
                             "same through mpccbf_step_batch_host_async returning all n control points per agent"},
             "gpu_launches": launches, "launched_with_cuda_graphs": used_graph,

@@ -375,336 +375,9 @@ __host__ __device__ int gi_run(GIState<D>& g, const Rows& rows, int max_iter, in
     return gi_run<D, false, Rows>(g, gs, rows, max_iter, n_iter, vmax2);
 }
 
-// =====================================================================================================================
-// Second core (CORE = 1): the same iteration with a PERSISTENT factorisation — orthogonal J and triangular R of the
-// active normals, updated by Givens rotations when a row enters or leaves (round 1's formulation). It executes fewer
-// instructions per step than re-factorising, at the price of 2 D^2 more live doubles across the row scans. Which core
-// the fused kernel uses is a measured choice (profiles/r2*_variants.md); both give the same minimiser.
-// =====================================================================================================================
-template <int D>
-struct GIStateJR {
-    double J[D][D];
-    double Rm[D][D];  // upper triangular, leading q x q block used
-    double u[D];      // multipliers of the active rows
-    double v[D];      // current iterate
-    int id[D];        // row id of each active column
-    int q;            // number of active rows
-};
-
-template <int D>
-MPCCBF_HD void gi_reset_factor_jr(GIStateJR<D>& g) {
-#pragma unroll
-    for (int i = 0; i < D; ++i) {
-#pragma unroll
-        for (int j = 0; j < D; ++j) {
-            g.J[i][j] = (i == j) ? 1.0 : 0.0;
-            g.Rm[i][j] = 0.0;
-        }
-    }
-}
-
-template <int D>
-MPCCBF_HD void gi_init_jr(GIStateJR<D>& g, const double* v0) {
-    gi_reset_factor_jr<D>(g);
-#pragma unroll
-    for (int i = 0; i < D; ++i) {
-        g.u[i] = 0.0;
-        g.v[i] = v0[i];
-        g.id[i] = -1;
-    }
-    g.q = 0;
-}
-
-// d = J' n
-template <int D>
-MPCCBF_HD void gi_project_jr(const GIStateJR<D>& g, const double (&np)[D], double (&d)[D]) {
-#pragma unroll
-    for (int j = 0; j < D; ++j) {
-        double s = 0.0;
-#pragma unroll
-        for (int i = 0; i < D; ++i) s = fma(g.J[i][j], np[i], s);
-        d[j] = s;
-    }
-}
-
-// Appends the column whose projection is d = J' n: rotates d[q..] onto e_q (Givens from the bottom,
-// carried into J2) and stores R's new column. The caller sets u / id of the new column.
-template <int D>
-MPCCBF_HD void gi_add_column_jr(GIStateJR<D>& g, double (&d)[D]) {
-#pragma unroll
-    for (int k = D - 1; k >= 1; --k) {
-        if (k > g.q) {
-            const double a = d[k - 1], b = d[k];
-            const double hh = sqrt(fma(a, a, b * b));
-            if (hh > 0.0) {
-                const double ih = 1.0 / hh;
-                const double cs = a * ih, sn = b * ih;
-                d[k - 1] = hh;
-                d[k] = 0.0;
-#pragma unroll
-                for (int i = 0; i < D; ++i) {
-                    const double a1 = g.J[i][k - 1], a2 = g.J[i][k];
-                    g.J[i][k - 1] = fma(cs, a1, sn * a2);
-                    g.J[i][k] = fma(-sn, a1, cs * a2);
-                }
-            }
-        }
-    }
-#pragma unroll
-    for (int col = 0; col < D; ++col)
-        if (col == g.q) {
-#pragma unroll
-            for (int i = 0; i <= col; ++i) g.Rm[i][col] = d[i];
-        }
-    ++g.q;
-}
-
-// Removes active column lpos (R becomes upper Hessenberg from there; Givens restore the triangle).
-template <int D>
-MPCCBF_HD void gi_drop_column_jr(GIStateJR<D>& g, int lpos) {
-#pragma unroll
-    for (int col = 0; col < D - 1; ++col)
-        if (col >= lpos) {
-#pragma unroll
-            for (int i = 0; i <= col + 1; ++i) g.Rm[i][col] = g.Rm[i][col + 1];  // Hessenberg part
-            g.u[col] = g.u[col + 1];
-            g.id[col] = g.id[col + 1];
-        }
-    g.u[D - 1] = 0.0;
-    g.id[D - 1] = -1;
-    --g.q;
-#pragma unroll
-    for (int k = 0; k < D - 1; ++k)
-        if (k >= lpos && k < g.q) {
-            const double a = g.Rm[k][k], b = g.Rm[k + 1][k];
-            const double hh = sqrt(fma(a, a, b * b));
-            if (hh > 0.0) {
-                const double ih = 1.0 / hh;
-                const double cs = a * ih, sn = b * ih;
-#pragma unroll
-                for (int col = 0; col < D; ++col)
-                    if (col >= k) {
-                        // (the sub-diagonal entry b is annihilated; it is never read again)
-                        const double a1 = g.Rm[k][col], a2 = (col > k) ? g.Rm[k + 1][col] : b;
-                        g.Rm[k][col] = fma(cs, a1, sn * a2);
-                        if (col > k) g.Rm[k + 1][col] = fma(-sn, a1, cs * a2);
-                    }
-#pragma unroll
-                for (int i = 0; i < D; ++i) {
-                    const double a1 = g.J[i][k], a2 = g.J[i][k + 1];
-                    g.J[i][k] = fma(cs, a1, sn * a2);
-                    g.J[i][k + 1] = fma(-sn, a1, cs * a2);
-                }
-            }
-        }
-}
-
-// J, R from the ids of the active columns (u, v, id, q are kept): QR of <= D normals.
-template <int D, class Rows>
-MPCCBF_HD void gi_rebuild_jr(GIStateJR<D>& g, const Rows& rows) {
-    const int q = g.q;
-    gi_reset_factor_jr<D>(g);
-    g.q = 0;
-#pragma unroll
-    for (int c = 0; c < D; ++c)
-        if (c < q) {
-            double np[D], rhs, d[D];
-            rows.normal(g.id[c], np, rhs);
-            gi_project_jr<D>(g, np, d);
-            gi_add_column_jr<D>(g, d);
-        }
-}
-
-// Rows must provide:
-//   void scan(const double (&v)[D], double& best, int& best_id) const;   best_id < 0: feasible;
-//        best = +inf flags a violated row that does not depend on v (infeasible)
-//   void normal(int id, double (&np)[D], double& rhs) const;             row  np.v >= rhs
-// and, for SOFT = true,
-//   int group(int id) const;            group of a row (-1: hard row)
-//   double weight(int group) const;     w_j
-//   void set_leader(int group, int id) const;   the piece `id` becomes the leader of its group
-// Returns a SolveStatus code; n_iter is incremented per active-set step.
-template <int D, bool SOFT, class Rows>
-__host__ __device__ int gi_run_jr(GIStateJR<D>& g, GISoft<D>& gs, const Rows& rows, int max_iter, int& n_iter, double vmax2) {
-    const double kInfD = HUGE_VAL;
-    for (;;) {
-        double best = 0.0;
-        int best_id = -1;
-        rows.scan(g.v, best, best_id);
-        if (best_id < 0) return MPCCBF_STATUS_OPTIMAL;
-        if (!(best < kInfD)) return MPCCBF_STATUS_INFEASIBLE;
-        double np[D], rhs;
-        rows.normal(best_id, np, rhs);
-        int pgrp = -1;
-        double pcap = kInfD;
-        if constexpr (SOFT) {
-            pgrp = rows.group(best_id);
-            if (pgrp >= 0) pcap = rows.weight(pgrp);
-        }
-
-        double up_mult = 0.0;
-        for (;;) {
-            if (++n_iter > max_iter) return MPCCBF_STATUS_ERROR;
-            double d[D];
-            gi_project_jr<D>(g, np, d);
-            // z = J2 d2, |d2|^2, |d|^2
-            double z[D];
-#pragma unroll
-            for (int i = 0; i < D; ++i) z[i] = 0.0;
-            double ztn = 0.0, dall = 0.0;
-#pragma unroll
-            for (int j = 0; j < D; ++j) {
-                dall = fma(d[j], d[j], dall);
-                if (j >= g.q) {
-                    ztn = fma(d[j], d[j], ztn);
-#pragma unroll
-                    for (int i = 0; i < D; ++i) z[i] = fma(g.J[i][j], d[j], z[i]);
-                }
-            }
-            // r = R^-1 d1
-            double rr[D];
-#pragma unroll
-            for (int i = D - 1; i >= 0; --i) {
-                double s = d[i];
-#pragma unroll
-                for (int k = i + 1; k < D; ++k)
-                    if (k < g.q) s = fma(-g.Rm[i][k], rr[k], s);
-                rr[i] = (i < g.q) ? s / g.Rm[i][i] : 0.0;
-            }
-            const double zt = 1e4 * 2.220446049250313e-16;
-            const bool z_zero = !(ztn > zt * zt * dall);
-            double t1 = kInfD;
-            int lpos = -1;
-#pragma unroll
-            for (int j = 0; j < D; ++j)
-                if (j < g.q && rr[j] > 0.0) {
-                    const double t = g.u[j] / rr[j];
-                    if (t < t1) {
-                        t1 = t;
-                        lpos = j;
-                    }
-                }
-            double sp = -rhs;
-#pragma unroll
-            for (int i = 0; i < D; ++i) sp = fma(np[i], g.v[i], sp);
-            const double t2 = z_zero ? kInfD : (-sp / ztn);
-            // third rule: a group's multiplier sum reaches its weight
-            double t3 = kInfD;
-            int g3 = -1;
-            if constexpr (SOFT) {
-                // entries: the entering row (rate +1, multiplier up_mult) and the active columns (rate -rr)
-#pragma unroll
-                for (int e = -1; e < D; ++e) {
-                    const int ge = (e < 0) ? pgrp : ((e < g.q) ? gs.grp[e] : -1);
-                    if (ge < 0) continue;
-                    bool first = !(e >= 0 && pgrp == ge);
-#pragma unroll
-                    for (int f = 0; f < D; ++f)
-                        if (f < e && f < g.q && gs.grp[f] == ge) first = false;
-                    if (!first) continue;
-                    double sum = (pgrp == ge) ? up_mult : 0.0, rate = (pgrp == ge) ? 1.0 : 0.0;
-#pragma unroll
-                    for (int f = 0; f < D; ++f)
-                        if (f < g.q && gs.grp[f] == ge) {
-                            sum += g.u[f];
-                            rate -= rr[f];
-                        }
-                    const double w = (e < 0) ? pcap : gs.cap[e];
-                    if (rate > 0.0) {
-                        const double tt = fmax(w - sum, 0.0) / rate;
-                        if (tt < t3) {
-                            t3 = tt;
-                            g3 = ge;
-                        }
-                    }
-                }
-            }
-            const double t = fmin(fmin(t1, t2), t3);
-            if (!(t < kInfD)) return MPCCBF_STATUS_INFEASIBLE;
-            if (!z_zero) {
-#pragma unroll
-                for (int i = 0; i < D; ++i) g.v[i] = fma(t, z[i], g.v[i]);
-            }
-#pragma unroll
-            for (int j = 0; j < D; ++j)
-                if (j < g.q) g.u[j] = fma(-t, rr[j], g.u[j]);
-            up_mult += t;
-            if (gi_diverged<D>(g.v, vmax2)) return MPCCBF_STATUS_INFEASIBLE;
-
-            if (!z_zero && t2 <= t1 && t2 <= t3) {
-                // full step: add the row
-#pragma unroll
-                for (int col = 0; col < D; ++col)
-                    if (col == g.q) {
-                        g.u[col] = up_mult;
-                        g.id[col] = best_id;
-                        if constexpr (SOFT) {
-                            gs.grp[col] = pgrp;
-                            gs.cap[col] = pcap;
-                        }
-                    }
-                gi_add_column_jr<D>(g, d);
-                break;
-            }
-            if constexpr (SOFT) if (t3 <= t1) {
-                // group g3 is at its weight: the leadership passes to the active row of the group with the
-                // largest multiplier, or to the entering row when the group has no active row
-                int a = -1;
-                double ua = -1.0;
-#pragma unroll
-                for (int c = 0; c < D; ++c)
-                    if (c < g.q && gs.grp[c] == g3 && g.u[c] > ua) {
-                        a = c;
-                        ua = g.u[c];
-                    }
-                if (a < 0) {  // no active row in the group: it is the entering row's own group
-                    rows.set_leader(g3, best_id);  // absorbed by its slack
-                    break;
-                }
-                int aid = -1;
-#pragma unroll
-                for (int c = 0; c < D; ++c)
-                    if (c == a) aid = g.id[c];
-                rows.set_leader(g3, aid);
-#pragma unroll
-                for (int c = 0; c < D - 1; ++c)
-                    if (c >= a) {
-                        g.u[c] = g.u[c + 1];
-                        g.id[c] = g.id[c + 1];
-                        gs.grp[c] = gs.grp[c + 1];
-                        gs.cap[c] = gs.cap[c + 1];
-                    }
-                g.u[D - 1] = 0.0;
-                g.id[D - 1] = -1;
-                gs.grp[D - 1] = -1;
-                --g.q;
-                gi_rebuild_jr<D>(g, rows);  // the group's other active rows are now expressed against the new leader
-                if (pgrp == g3) rows.normal(best_id, np, rhs);
-                continue;
-            }
-            // partial (or dual-only) step: drop active row lpos
-            if constexpr (SOFT) {
-#pragma unroll
-                for (int c = 0; c < D - 1; ++c)
-                    if (c >= lpos) {
-                        gs.grp[c] = gs.grp[c + 1];
-                        gs.cap[c] = gs.cap[c + 1];
-                    }
-                gs.grp[D - 1] = -1;
-            }
-            gi_drop_column_jr<D>(g, lpos);
-        }
-    }
-}
-
-
-template <int D, class Rows>
-__host__ __device__ int gi_run_jr(GIStateJR<D>& g, const Rows& rows, int max_iter, int& n_iter, double vmax2 = HUGE_VAL) {
-    GISoft<D> gs;
-    return gi_run_jr<D, false, Rows>(g, gs, rows, max_iter, n_iter, vmax2);
-}
-
-// core selection by a compile-time index
+// The fused kernel reaches the solver through GICore<D, CORE>. CORE = 0 is the re-factorising iteration above. A second
+// core that kept a persistent orthogonal / triangular factorisation updated by Givens rotations (round 1's formulation)
+// was measured 1.7x slower (profiles/r2_kernel_ab.md) and has been removed; the parameter stays for experiments.
 template <int D, int CORE>
 struct GICore;
 template <int D>
@@ -717,17 +390,6 @@ struct GICore<D, 0> {
     }
     template <class Rows>
     MPCCBF_HD static void refactor(State& g, const Rows& rows) { gi_refresh<D>(g, rows); }
-};
-template <int D>
-struct GICore<D, 1> {
-    typedef GIStateJR<D> State;
-    MPCCBF_HD static void init(State& g, const double* v0) { gi_init_jr<D>(g, v0); }
-    template <bool SOFT, class Rows>
-    MPCCBF_HD static int run(State& g, GISoft<D>& gs, const Rows& rows, int max_iter, int& n_iter, double vmax2) {
-        return gi_run_jr<D, SOFT, Rows>(g, gs, rows, max_iter, n_iter, vmax2);
-    }
-    template <class Rows>
-    MPCCBF_HD static void refactor(State& g, const Rows& rows) { gi_rebuild_jr<D>(g, rows); }
 };
 
 }  // namespace mpccbf

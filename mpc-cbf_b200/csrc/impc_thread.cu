@@ -1169,13 +1169,12 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
         c.fied = (T.conn_mode && a.fiedler) ? a.fiedler + static_cast<size_t>(scen) * T.N : nullptr;
         c.conn = connrows.data();
         c.lead = lead.data();
-        static const int core = [] { const char* e = std::getenv("MPCCBF_THREAD_CORE"); return e ? std::atoi(e) : MPCCBF_THREAD_CORE; }();
         if (T.slack) {
-            if (core == 1) agent_thread<true, false, 1>(T, a, g, self, c); else agent_thread<true, false, 0>(T, a, g, self, c);
+            agent_thread<true, false, 0>(T, a, g, self, c);
         } else if (T.conn_mode) {
-            if (core == 1) agent_thread<false, true, 1>(T, a, g, self, c); else agent_thread<false, true, 0>(T, a, g, self, c);
+            agent_thread<false, true, 0>(T, a, g, self, c);
         } else {
-            if (core == 1) agent_thread<false, false, 1>(T, a, g, self, c); else agent_thread<false, false, 0>(T, a, g, self, c);
+            agent_thread<false, false, 0>(T, a, g, self, c);
         }
         if (a.v_out)
             for (int i = 0; i < 6; ++i) a.v_out[static_cast<size_t>(g) * 6 + i] = sol[i * kLS];
@@ -1218,23 +1217,22 @@ int launch_impc_thread(const DevTables& T, const StepArgs& a, int sm_count, cuda
 #endif
     if (T.slack && !a.lead_ws) return cudaErrorInvalidValue;
     if (T.conn_mode && (!a.lambda2 || !a.fiedler)) return cudaErrorInvalidValue;
-    // Active-set core and launch shape: measured defaults (profiles/r2*_variants.md); MPCCBF_THREAD_CORE = 0 / 1 and
+    // Launch shape: measured default (profiles/r2_kernel_ab.md);
     // MPCCBF_THREAD_CFG = 0 / 2 / 3 / 4 override them for experiments.
-    static const int core = [] { const char* e = std::getenv("MPCCBF_THREAD_CORE"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CORE; return v == 1 ? 1 : 0; }();
     static const int cfgi = [] { const char* e = std::getenv("MPCCBF_THREAD_CFG"); const int v = e ? std::atoi(e) : MPCCBF_THREAD_CFG; return (v >= 2 && v <= 4) ? v : 0; }();
     ThreadKernel kern;
     int threads;
     if (cfgi == 2) {
-        kern = core ? pick_kernel<1, 2>(T) : pick_kernel<0, 2>(T);
+        kern = pick_kernel<0, 2>(T);
         threads = ThreadCfg<2>::kThreads;
     } else if (cfgi == 3) {
-        kern = core ? pick_kernel<1, 2>(T) : pick_kernel<0, 2>(T);
+        kern = pick_kernel<0, 2>(T);
         threads = ThreadCfg<3>::kThreads;
     } else if (cfgi == 4) {   // 224 x 2 at 128 registers: 159 KB of shared memory per SM, i.e. the 164 KB carve-out (L1 64 KB)
         kern = T.slack ? impc_thread_kernel_b224<true, false, 0, 0> : (T.conn_mode ? impc_thread_kernel_b224<false, true, 0, 0> : impc_thread_kernel_b224<false, false, 0, 0>);
         threads = 224;
     } else {
-        kern = core ? pick_kernel<1, 0>(T) : pick_kernel<0, 0>(T);
+        kern = pick_kernel<0, 0>(T);
         threads = ThreadCfg<0>::kThreads;
     }
     // Agents per warp. The kernel is latency-bound (its duration is that of its slowest warp, ~5 us per active-set step of

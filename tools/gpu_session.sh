@@ -7,7 +7,7 @@ O=gpurun_out
 mkdir -p $O
 echo "== kernel variants (device leg only)"
 : > $O/${TAG}_variants.jsonl
-for core in 0 1; do for cfg in 0 2 3 4; do
+for core in 0; do for cfg in 0 2 3 4; do
   MPCCBF_THREAD_CORE=$core MPCCBF_THREAD_CFG=$cfg python bench.py --steps 48 --warmup 8 --device-only --no-extras --no-cpu-baseline >> $O/${TAG}_variants.jsonl 2>> $O/${TAG}_bench.err
 done; done
 python - <<PY
