@@ -49,6 +49,10 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the weak-scaling and sharded-cfg4 sub-records")
     ap.add_argument("--device-only", action="store_true", help="skip the end-to-end legs (kernel variant comparisons)")
+    ap.add_argument("--device-streams", type=int, default=1, choices=[1, 2],
+                    help="device leg: 1 = every step after the previous one on one stream (default); 2 = consecutive "
+                         "(independent) steps alternate between two streams / handles, joined once per pass over the snapshot "
+                         "sets (measured slower: 0.197 vs 0.182 ms per step)")
     ap.add_argument("--e2e-depth", type=int, default=3, help="batches in flight in the end-to-end leg (one handle each)")
     ap.add_argument("--no-graph", action="store_true", help="launch every timed step from Python instead of CUDA graphs")
     ap.add_argument("--seed", type=int, default=20261104)
@@ -305,6 +309,11 @@ class DeviceLeg:
                                   nxt=torch.empty_like(cur)))
         self.stream = torch.cuda.Stream(device=dev)
         self.sp = self.stream.cuda_stream
+        # second lane for the timed loop: consecutive steps are independent batches, so odd steps run on a second stream
+        # through a second handle (its own workspaces) and the kernels of neighbouring steps fill each other's tails
+        self.lanes = 1 if args.device_streams <= 1 else 2
+        self.h2 = M.Handle(self.cfg) if self.lanes == 2 else None
+        self.stream2 = torch.cuda.Stream(device=dev) if self.lanes == 2 else None
         h, sp = self.h, self.sp
         with torch.cuda.stream(self.stream):
             for i in range(self.R * SNAP_STRIDE):
@@ -317,10 +326,27 @@ class DeviceLeg:
         self.set_bytes = sum(t.numel() * t.element_size() for t in self.sets[0].values())
         self.graph = None
 
-    def step(self, i):
+    def step(self, i, lane=0):
         b = self.sets[i % self.R]
-        self.h.step_batch(self.S, b["states"], self.d_tg, b["ctrl"], b["status"], b["n_curves"], b["objective"], stream=self.sp)
-        self.h.rollout(self.S, b["states"], b["ctrl"], b["n_curves"], b["nxt"], stream=self.sp)
+        h, sp = (self.h, self.sp) if lane == 0 else (self.h2, self.stream2.cuda_stream)
+        h.step_batch(self.S, b["states"], self.d_tg, b["ctrl"], b["status"], b["n_curves"], b["objective"], stream=sp)
+        h.rollout(self.S, b["states"], b["ctrl"], b["n_curves"], b["nxt"], stream=sp)
+
+    def one_pass(self):
+        """The R steps of a pass: on one stream, or alternating between two that fork from and join the main stream."""
+        torch = self.torch
+        if self.lanes == 1:
+            for i in range(self.R):
+                self.step(i)
+            return
+        self.stream2.wait_stream(self.stream)
+        for i in range(self.R):
+            if i % 2 == 0:
+                self.step(i, 0)
+            else:
+                with torch.cuda.stream(self.stream2):
+                    self.step(i, 1)
+        self.stream.wait_stream(self.stream2)
 
     def capture(self):
         """One CUDA graph = one pass over the R snapshot sets (R steps): the timed loop replays it, so that the
@@ -328,12 +354,10 @@ class DeviceLeg:
         torch = self.torch
         g = torch.cuda.CUDAGraph()
         with torch.cuda.stream(self.stream):
-            for i in range(self.R):
-                self.step(i)
+            self.one_pass()
         self.stream.synchronize()
         with torch.cuda.graph(g, stream=self.stream):
-            for i in range(self.R):
-                self.step(i)
+            self.one_pass()
         self.graph = g
 
     def run_steps(self, first, count):
@@ -344,6 +368,9 @@ class DeviceLeg:
                 if self.graph is not None and i % self.R == 0 and end - i >= self.R:
                     self.graph.replay()
                     i += self.R
+                elif self.graph is None and self.lanes == 2 and i % self.R == 0 and end - i >= self.R:
+                    self.one_pass()
+                    i += self.R
                 else:
                     self.step(i)
                     i += 1
@@ -351,6 +378,8 @@ class DeviceLeg:
     def close(self):
         self.graph = None
         self.h.close()
+        if self.h2 is not None:
+            self.h2.close()
 
 
 def time_device(torch, leg, args, barrier, max_over_ranks):
@@ -528,6 +557,12 @@ def run_b200(args):
         clocks.start()
     total_ms, launches, used_graph, lib_launches = time_device(torch, leg, args, barrier, max_over_ranks)
     value = qps_total * args.steps / (total_ms * 1e-3)
+    one_stream = None
+    if leg.lanes == 2:   # the same K steps strictly one after the other on one stream, for comparison
+        leg.lanes, leg.graph = 1, None
+        s_ms, _, _, _ = time_device(torch, leg, args, barrier, max_over_ranks)
+        leg.lanes, leg.graph = 2, None
+        one_stream = {"value": qps_total * args.steps / (s_ms * 1e-3), "ms_per_step": s_ms / args.steps}
     step_ms, kern_ms = step_latency(torch, leg, max(16, min(args.steps, 64)))
     # ---- end to end ----------------------------------------------------------------------------------------------
     if args.device_only:
@@ -535,6 +570,7 @@ def run_b200(args):
         if rank == 0:
             print(json.dumps({"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                               "ms_per_step": total_ms / args.steps, "kernel_ms": kern_ms, "p50_step_ms": float(np.median(step_ms)),
+                              "one_stream": one_stream,
                               "variant": {"core": os.environ.get("MPCCBF_THREAD_CORE"), "cfg": os.environ.get("MPCCBF_THREAD_CFG")},
                               "e2e": None, "clocks": clk, "note": "--device-only: kernel variant comparison, not a bench line"}), flush=True)
         leg.close()
@@ -562,7 +598,7 @@ def run_b200(args):
             flops += float(np.sum(r_dof ** 3 / 3 + m_cbf * 8 * r_dof + m_cbf * r_dof ** 2
                                   + gi[:, it_idx] * (4 * m_rows * r_dof + 2 * r_dof ** 2))) / len(leg.sets)
         mean_iters += float(gi.mean()) / len(leg.sets)
-    set_bytes, R = leg.set_bytes, leg.R
+    set_bytes, R, leg_lanes = leg.set_bytes, leg.R, leg.lanes
     snaps_h = [b["states"].cpu().numpy() for b in leg.sets] if (rank == 0 and not args.no_cpu_baseline) else None
     tg_h = leg.tg_h
     leg.close()
@@ -646,10 +682,15 @@ def run_b200(args):
             "gpu_launches": launches, "launched_with_cuda_graphs": used_graph,
             "p50_step_ms": float(np.median(step_ms)), "p99_step_ms": float(np.percentile(step_ms, 99)),
             "solved_value": value * solved_frac,
+            "device_streams": leg_lanes, "one_stream": one_stream,
             "details": {"scenarios_this_rank": S, "qps_per_step_per_gpu": S * N * iters,
                         "status_counts_all_snapshots_rank0": counts,
                         "note_value": "value counts every (agent, IMPC iteration) slot like the reference's loop does; "
-                                      "solved_value excludes the SKIPPED slots (iteration after a failed one)",
+                                      "solved_value excludes the SKIPPED slots (iteration after a failed one). The K timed "
+                                      "steps are independent batches: with device_streams = 2 consecutive steps alternate "
+                                      "between two streams (joined once per pass over the snapshot sets) so that their "
+                                      "kernels fill each other's tails; one_stream = the same K steps strictly in sequence; "
+                                      "roofline.kernel_ms is one launch alone",
                         "snapshot_bytes_rank0": R * set_bytes, "affinity": affinity},
             "roofline": roofline, "cpu_baseline": cpu, "clocks": clk}
     if weak is not None:
