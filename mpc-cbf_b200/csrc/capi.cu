@@ -393,7 +393,7 @@ int resolve_lanes(const mpccbf_handle* h, int64_t num_qp, bool force_auto = fals
         // its warps fit in two waves of 8 per SM (2368 agents: 0.094 vs 0.127 ms at 2048 agents, a tie at 4096); the
         // thread-per-agent kernel wins beyond. The 8-lane variant is only the large-batch fallback for configurations
         // without the polynomial row structure.
-        const int wave = 16 * h->sm_count;
+        const int wave = 16 * h->sm_count * (h->cfg.num_agents >= 128 ? 2 : 1);   // dense swarms: a scan walks hundreds of rows
         lanes = (num_qp <= wave) ? 32 : 0;
     }
     if (h->cfg.slack_mode || h->cfg.conn_mode) lanes = 0;  // capped multipliers / lifted connectivity rows: thread-per-agent kernel only

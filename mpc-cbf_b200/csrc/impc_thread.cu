@@ -36,7 +36,8 @@ namespace mpccbf {
 #ifndef MPCCBF_CAND_MAX
 #define MPCCBF_CAND_MAX 16
 #endif
-constexpr int kCandMax = MPCCBF_CAND_MAX;   // candidate safety rows kept per agent (more: scan all rows)
+constexpr int kCandMaxSmall = MPCCBF_CAND_MAX;   // candidate safety rows kept per agent (more: scan all rows) for swarms of <= 32
+constexpr int kCandMaxLarge = 32;                // agents, and for larger ones (their scenario states dominate the block anyway)
 constexpr int kSolStride = 7;  // per-agent result record: v[6] (whitened free dof of the last successful iterate), n_ok
 constexpr int kNcRows = 16;    // normals of the <= 4 active rows of the x / y problem (gi_solver.h: GIState::nc)
 // Per-agent scratch is LANE-STRIDED: element i of an array belongs to lane l at [i * kLS + l] (doubles), and the arrays
@@ -47,8 +48,8 @@ static_assert(kLS == kNcStride, "the normal cache of gi_solver.h is lane-strided
 constexpr int kRow = kLS * 8;                          // bytes of one lane-strided row
 constexpr int kOffSol = 0;
 constexpr int kOffNc = kOffSol + kSolStride * kRow;
-constexpr int kOffCand = kOffNc + kNcRows * kRow;      // kCandMax rows of kLS unsigned shorts
-constexpr int kOffPred = kOffCand + kCandMax * kLS * 2;  // H * 4 rows; then (conn_mode) H * 3 rows, Fiedler vectors; scenario states
+constexpr int kOffPred = kOffNc + kNcRows * kRow;      // H * 4 rows; then the candidate list (cand_max rows of kLS unsigned shorts),
+                                                       // (conn_mode) H * 3 rows, Fiedler vectors; scenario states
 // CTA-shared tables at compile-time offsets from the start of shared memory (doubles): pq[5][4], lim[3][8], scn[K][4];
 // the horizon-sized tables follow (ThreadSmemLayout)
 constexpr int kOffLim = 20, kOffScn = 44;
@@ -311,6 +312,7 @@ struct RowsXY {
     const double* pred;   // ego states per horizon step: pred[(k*4 + c) * kLS], c = px,py,vx,vy
     const unsigned short* cand;  // candidate row ids: cand[i * kLS]
     int ncand;            // < 0: scan all `ncbf` rows
+    int cand_max;         // capacity of the candidate list
     int ncbf, hit, self;  // ncbf pairwise rows: [0, nsafe) safety HOCBF, [nsafe, ncbf) distance CLF (conn_mode, lambda2 <= 0.1)
     int nsafe;            // (N - 1) * hit
     int nconn;            // connectivity HOCBF rows (conn_mode, lambda2 > 0.1): row ids ncbf + k, values in conn[]
@@ -523,6 +525,7 @@ struct AgentCtx {
     const double* st;                 // this agent's scenario states [N][6]
     double* pred;                     // [(k*4 + c) * kLS]
     unsigned short* cand;             // [i * kLS]
+    int cand_max;
     double* sol;                      // [kSolStride * kLS] result record of this agent
     double* nc;                       // [kNcRows * kLS] normals of the active rows (GIState::nc)
     unsigned char* lead;              // [N-1] group leaders of this agent (slack mode), else NULL
@@ -560,12 +563,12 @@ MPCCBF_HD void build_candidates(RowsXY<SOFT, CONN>& rx, const DevTables& T, unsi
             if (fill && keep && j < rx.nsafe) k0mask |= 1ull << j;
         }
         if (keep) {
-            if (nc < kCandMax) cand[nc * kLS] = static_cast<unsigned short>(j);
+            if (nc < rx.cand_max) cand[nc * kLS] = static_cast<unsigned short>(j);
             ++nc;
         }
     }
     if (fill) k0valid = true;
-    rx.ncand = (wide || nc > kCandMax) ? -1 : nc;
+    rx.ncand = (wide || nc > rx.cand_max) ? -1 : nc;
 }
 
 MPCCBF_HD double ctrl_point(const double* y, double ps, double vs, double va, double vb) {
@@ -657,6 +660,7 @@ __host__ __device__ void agent_thread(const DevTables& T, const StepArgs& a, int
     rx.st = c.st;
     rx.pred = c.pred;
     rx.cand = c.cand;
+    rx.cand_max = c.cand_max;
     rx.ncand = 0;
     rx.ncbf = 0;
     rx.nsafe = 0;
@@ -970,6 +974,7 @@ struct ThreadSmemLayout {
     int off_tm, off_vr, off_kr, off_yw, off_omap;
     int n_tm, n_yw, n_vr;
     // per warp (bytes from the warp's block): the fixed-offset arrays (kOffSol .. kOffPred), then
+    int off_cand, cand_max;          // candidate list and its capacity
     int off_conn, off_fied, off_st;  // conn_mode rows and Fiedler vectors (empty otherwise), scenario states
     int n_fied;
     int apw;                         // agents per warp (a tile): 32, or fewer so that a small batch still fills the SMs
@@ -993,7 +998,9 @@ static ThreadSmemLayout thread_layout(const DevTables& T, int agent_count, int a
     const int ac = std::max(agent_count, 1);
     L.nscen_max = (apw % ac == 0) ? apw / ac : (ac % apw == 0 ? 1 : (apw - 1) / ac + 2);
     const int H = std::max(T.H, 1);
-    L.off_conn = kOffPred + H * 4 * kRow;
+    L.cand_max = (T.N <= 32) ? kCandMaxSmall : kCandMaxLarge;
+    L.off_cand = kOffPred + H * 4 * kRow;
+    L.off_conn = L.off_cand + L.cand_max * kLS * 2;
     L.off_fied = L.off_conn + (T.conn_mode ? H * 3 * kRow : 0);
     L.n_fied = T.conn_mode ? L.nscen_max * T.N : 0;
     L.off_st = (L.off_fied + 8 * L.n_fied + 15) / 16 * 16;
@@ -1098,7 +1105,8 @@ __device__ __forceinline__ void thread_kernel_body(const DevTables& T, const Ste
             unsigned char* tb = wbase + lane * 8;   // every lane-strided array of this agent: tb + immediate
             c.sol = reinterpret_cast<double*>(tb + kOffSol);
             c.nc = reinterpret_cast<double*>(tb + kOffNc);
-            c.cand = reinterpret_cast<unsigned short*>(wbase + kOffCand) + lane;
+            c.cand = reinterpret_cast<unsigned short*>(wbase + L.off_cand) + lane;
+            c.cand_max = L.cand_max;
             c.pred = reinterpret_cast<double*>(tb + kOffPred);
             c.conn = reinterpret_cast<double*>(tb + L.off_conn);
             c.lam2 = L.n_fied ? __ldg(a.lambda2 + scen) : 0.0;
@@ -1147,7 +1155,7 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
     // the same lane-strided scratch layout as a warp of the kernel, used by lane 0
     const int H = std::max(T.H, 1);
     std::vector<double> pred(static_cast<size_t>(H) * 4 * kLS), sol(static_cast<size_t>(kSolStride) * kLS);
-    std::vector<unsigned short> cand(static_cast<size_t>(kCandMax) * kLS);
+    std::vector<unsigned short> cand(static_cast<size_t>(kCandMaxLarge) * kLS);
     std::vector<double> ncache(static_cast<size_t>(kNcRows) * kLS), connrows(static_cast<size_t>(H) * 3 * kLS);
     std::vector<double> lim(24), scn(static_cast<size_t>(4) * T.K);
     std::vector<unsigned char> lead(static_cast<size_t>(std::max(T.N, 1)));
@@ -1163,6 +1171,7 @@ void emul_impc_thread_host(const DevTables& T, const StepArgs& a) {
         c.st = a.states + static_cast<size_t>(scen) * T.N * 6;
         c.pred = pred.data();
         c.cand = cand.data();
+        c.cand_max = (T.N <= 32) ? kCandMaxSmall : kCandMaxLarge;
         c.sol = sol.data();
         c.nc = ncache.data();
         c.lam2 = (T.conn_mode && a.lambda2) ? a.lambda2[scen] : 0.0;
