@@ -39,7 +39,7 @@ ncu --set full --clock-control none --import-source on -k regex:impc_reduced_ker
     python bench.py --scenarios 1 --agents 8 --steps 4 --warmup 3 --no-extras --no-cpu-baseline --no-graph --device-only > $O/${TAG}_ncu_lanes.log 2>&1
 tail -2 $O/${TAG}_ncu_lanes.log
 echo "== ncu full, sub-kernels (rows, rollout, filter, episode, dense)"
-ncu --set full --clock-control none -k regex:"cbf_rows_kernel|rollout_kernel|cbf_filter_kernel|episode_advance_kernel|dense_qp_kernel" -c 8 -f -o $O/${TAG}_subkernels \
+ncu --set full --clock-control none -k regex:"cbf_rows_kernel|rollout_kernel|cbf_filter_kernel|episode_advance_kernel|dense_qp_kernel" -c 40 -f -o $O/${TAG}_subkernels \
     python bench_kernels.py --out $O/${TAG}_kernels_ncu.jsonl > $O/${TAG}_ncu_sub.log 2>&1
 tail -1 $O/${TAG}_ncu_sub.log
 echo "== reference arm"; python bench.py --impl reference --steps 20 --warmup 5 > $O/${TAG}_bench_ref.json 2>> $O/${TAG}_bench.err; cut -c1-200 $O/${TAG}_bench_ref.json
