@@ -452,10 +452,10 @@ def time_e2e(torch, M, leg, args, barrier, max_over_ranks, compact):
     for i in range(max(args.warmup, 2 * D)):
         call(hh[i % D], hs_np[i % R], oo[i % D])
         hh[i % D].synchronize()
-    # the K-step loop is run twice (a single host-side hiccup of ~100 ms is several steps' worth at K = 20); the
-    # better of the two repetitions is reported, both are listed, and so is the median step-to-step interval
+    # the K-step loop is run three times (the whole loop lasts ~8 ms at K = 48: one host-side hiccup is several steps'
+    # worth); the best repetition is reported, all are listed, and so is the median step-to-step interval
     reps, gaps = [], []
-    for rep in range(2):
+    for rep in range(3):
         barrier()
         t0 = time.perf_counter()
         last = t0
