@@ -245,7 +245,8 @@ int mpccbf_cbf_rows(mpccbf_handle* h, int32_t num_scenarios, const double* state
  *   u         [S][N][3]   filtered input; zeros where the QP is not OPTIMAL (the reference example
  *                         falls back to zero control: CBFFormationControl_example.cpp:168-172)
  *   status    [S][N]      SolveStatus;  lambda2 [S] algebraic connectivity (may be NULL)
- * One warp per scenario: num_agents <= 32, else MPCCBF_ERR_UNSUPPORTED. Uses cfg d_min, d_max,
+ * num_agents <= 32: one warp per scenario, matrices of the eigen-solve in shared memory; 33 .. 256: one CTA per scenario,
+ * matrices in a handle-owned workspace allocated on the first such call; beyond: MPCCBF_ERR_UNSUPPORTED. Uses cfg d_min, d_max,
  * cbf_gamma, v_min, v_max, feas_tol, and slack_mode / slack_cost / slack_decay: in slack mode
  * (ConnectivityControl.cpp:30-45) slack i (cost slack_cost * slack_decay^i) relaxes safety row i and CLF row i,
  * the last slack the connectivity row; the velocity rows stay hard. Device pointers, async on `cuda_stream`. */
@@ -259,7 +260,7 @@ int mpccbf_cbf_filter_batch_host(mpccbf_handle* h, int32_t num_scenarios, const 
 /* Sub-kernel: lambda2 and the connectivity HOCBF row of every agent ==
  * ConnectivityCBF::getLambda2 / initConnCBF / getConnConstraints / getConnBound
  * (cbf/src/detail/ConnectivityCBF.cpp:388-424,472-552). rows [S][N][4] = (ax, ay, az = 0, b) meaning
- * a.u + b >= 0; lambda2 [S]. Device pointers, async on stream. num_agents <= 32. */
+ * a.u + b >= 0; lambda2 [S]. Device pointers, async on stream. num_agents <= 256. */
 int mpccbf_conn_rows(mpccbf_handle* h, int32_t num_scenarios, const double* states, double* rows,
                      double* lambda2, void* cuda_stream);
 

@@ -53,6 +53,8 @@ struct mpccbf_handle {
     // slack mode (cbf_params.slack_mode): capped multipliers inside the fused thread-per-agent kernel
     // (gi_solver.h); scratch = one leader byte per (agent, neighbour)
     unsigned char* w_lead = nullptr;
+    void* w_filter = nullptr;   // workspace of the CBF-only filter for swarms of 33..256 agents (allocated on first use)
+    int w_filter_blocks = 0;
     // conn_mode: lambda2 [S] and Fiedler vector [S][N] of every scenario (cbf_filter.cu), refreshed before every step
     double *w_lam2 = nullptr, *w_fied = nullptr;
     std::vector<double> hc_lam2, hc_fied;  // host-only handles (tests/emul)
@@ -461,6 +463,20 @@ __global__ void dfma_peak_kernel(double* out, int iters, double a, double b) {
     if (s == 123.456) out[0] = s;  // keeps the chain alive without a store in practice
 }
 
+// Workspace of the CBF-only filter for swarms of more than 32 agents: Laplacian + eigenvector matrix (and slack-mode leaders)
+// of every resident CTA, 2 CTAs per SM, allocated on the first call that needs it.
+int ensure_filter_ws(mpccbf_handle* h) {
+    if (h->cfg.num_agents <= 32 || h->w_filter) return MPCCBF_OK;
+    const int blocks = std::max(1, std::min(h->cfg.max_scenarios, 2 * h->sm_count));
+    if (cudaMalloc(&h->w_filter, cbf_filter_wide_ws_bytes(h->cfg, blocks)) != cudaSuccess) {
+        h->w_filter = nullptr;
+        set_error("CBF-only filter: cudaMalloc of the eigen-solve workspace failed");
+        return MPCCBF_ERR_ALLOC;
+    }
+    h->w_filter_blocks = blocks;
+    return MPCCBF_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -608,6 +624,7 @@ int mpccbf_destroy(mpccbf_handle* h) {
         for (void* q : eptrs)
             if (q) cudaFree(q);
         if (h->w_lead) cudaFree(h->w_lead);
+        if (h->w_filter) cudaFree(h->w_filter);
         if (h->w_lam2) cudaFree(h->w_lam2);
         if (h->pin_in) cudaFreeHost(h->pin_in);
         if (h->pin_out) cudaFreeHost(h->pin_out);
@@ -1030,13 +1047,15 @@ int mpccbf_cbf_filter_batch(mpccbf_handle* h, int32_t S, const double* states, c
         set_error("mpccbf_cbf_filter_batch: invalid argument");
         return MPCCBF_ERR_INVALID;
     }
-    if (h->cfg.num_agents > 32) {
-        set_error("mpccbf_cbf_filter_batch: one lane per agent, num_agents must be <= 32");
+    if (h->cfg.num_agents > 256) {
+        set_error("mpccbf_cbf_filter_batch: num_agents must be <= 256 (one thread per agent of a scenario's CTA)");
         return MPCCBF_ERR_UNSUPPORTED;
     }
     CUDA_TRY(cudaSetDevice(h->device));
+    rc = ensure_filter_ws(h);
+    if (rc != MPCCBF_OK) return rc;
     CUDA_TRY(launch_cbf_filter(h->cfg, S, states, desired_u, u, status, lambda2, nullptr, h->sm_count,
-                               static_cast<cudaStream_t>(cuda_stream)));
+                               static_cast<cudaStream_t>(cuda_stream), nullptr, h->w_filter, h->w_filter_blocks));
     h->launches += 1;
     h->qps += static_cast<int64_t>(S) * h->cfg.num_agents;
     return MPCCBF_OK;
@@ -1074,13 +1093,15 @@ int mpccbf_conn_rows(mpccbf_handle* h, int32_t S, const double* states, double* 
         set_error("mpccbf_conn_rows: invalid argument");
         return MPCCBF_ERR_INVALID;
     }
-    if (h->cfg.num_agents > 32) {
-        set_error("mpccbf_conn_rows: one lane per agent, num_agents must be <= 32");
+    if (h->cfg.num_agents > 256) {
+        set_error("mpccbf_conn_rows: num_agents must be <= 256");
         return MPCCBF_ERR_UNSUPPORTED;
     }
     CUDA_TRY(cudaSetDevice(h->device));
+    rc = ensure_filter_ws(h);
+    if (rc != MPCCBF_OK) return rc;
     CUDA_TRY(launch_cbf_filter(h->cfg, S, states, nullptr, nullptr, nullptr, lambda2, rows, h->sm_count,
-                               static_cast<cudaStream_t>(cuda_stream)));
+                               static_cast<cudaStream_t>(cuda_stream), nullptr, h->w_filter, h->w_filter_blocks));
     h->launches += 1;
     return MPCCBF_OK;
 }

@@ -82,7 +82,7 @@ struct FilterRows {
             double np[2], rhs;
             row(id, np, rhs);
             const double viol = rhs - fma(np[0], v[0], np[1] * v[1]);
-            if (viol > tol * fmax(1.0, fabs(rhs)) && fabs(rhs) < 1e20) {
+            if (viol > tol * fmax(1.0, fabs(rhs)) && rhs > -1e20) {   // only an upper bound >= 1e20 (rhs <= -1e20 here) is "no bound"
                 const double n2 = fma(np[0], np[0], np[1] * np[1]);
                 const double score = (n2 > 0.0) ? viol * rsqrt(n2) : HUGE_VAL;
                 if (score > best) {
@@ -212,6 +212,79 @@ struct FilterArgs {
     double slack_cost, slack_decay;
 };
 
+// Everything after the eigen-solve for ONE agent: its connectivity HOCBF row (closed form), the safety / velocity / CLF
+// rows and the 3-variable QP (2-dof active-set projection for x / y, a clamp for yaw). st: the scenario's states [N][6],
+// fv: the normalised eigenvector of lambda2, lead: N bytes of scratch for this agent (slack mode).
+__device__ __forceinline__ void filter_agent(const FilterArgs& a, const double* st, const double* fv, double lam2, double R2,
+                                             double sigma, int s, int self, unsigned char* lead) {
+    const int N = a.N;
+    const size_t g = static_cast<size_t>(s) * N + self;
+    const double* e = st + self * 6;
+    // connectivity HOCBF row (closed form; eigenvector held constant, no range gating)
+    double gx = 0.0, gy = 0.0, hxx = 0.0, hxy = 0.0, hyy = 0.0;
+    for (int j = 0; j < N; ++j) {
+        if (j == self) continue;
+        const double dx = e[0] - st[j * 6], dy = e[1] - st[j * 6 + 1];
+        const double diff = R2 - (dx * dx + dy * dy);
+        const double E = exp(diff * diff / sigma);
+        const double dvj = fv[self] - fv[j], wj = dvj * dvj;
+        const double c = -4.0 * E * diff / sigma;
+        const double cp2 = 2.0 * (4.0 * E / sigma * (2.0 * diff * diff / sigma + 1.0));
+        gx = fma(c * wj, dx, gx);
+        gy = fma(c * wj, dy, gy);
+        hxx += wj * (c + cp2 * dx * dx);
+        hxy += wj * (cp2 * dx * dy);
+        hyy += wj * (c + cp2 * dy * dy);
+    }
+    const double vx = e[3], vy = e[4];
+    const double lfh = gx * vx + gy * vy;
+    const double lf2h = vx * (hxx * vx + hxy * vy) + vy * (hxy * vx + hyy * vy);
+    const double bconn = lf2h + a.gamma * lfh + a.gamma * (lfh + a.gamma * (lam2 - 0.1));
+    if (a.conn_rows) {
+        double* r = a.conn_rows + g * 4;
+        r[0] = gx; r[1] = gy; r[2] = 0.0; r[3] = bconn;
+    }
+    if (a.u && a.desired_u) {
+        const double* du = a.desired_u + g * 3;
+        FilterRows rows;
+        rows.st = st; rows.N = N; rows.self = self;
+        rows.dmin2 = a.dmin2; rows.gamma = a.gamma; rows.tol = a.tol;
+        rows.vlo[0] = -(e[3] - a.vmin[0]); rows.vhi[0] = a.vmax[0] - e[3];
+        rows.vlo[1] = -(e[4] - a.vmin[1]); rows.vhi[1] = a.vmax[1] - e[4];
+        rows.use_conn = lam2 > 0.1;
+        rows.gx = gx; rows.gy = gy; rows.bconn = bconn;
+        GIState<2> gi;
+        const double v0[2] = {__ldg(du), __ldg(du + 1)};
+        gi_init<2>(gi, v0);
+        int iters = 0;
+        int stat;
+        if (a.slack) {
+            // leaders of this agent's groups: N bytes provided by the caller
+            FilterRowsSoft soft;
+            soft.r = rows;
+            soft.lead = lead;
+            soft.slack_cost = a.slack_cost;
+            soft.slack_decay = a.slack_decay;
+            for (int gq = 0; gq < N; ++gq) soft.lead[gq] = 0;
+            GISoft<2> gs;
+            gs.grp[0] = gs.grp[1] = -1;
+            gs.cap[0] = gs.cap[1] = HUGE_VAL;
+            stat = gi_run<2, true, FilterRowsSoft>(gi, gs, soft, a.max_gi, iters, gi_vmax2<2>(v0));
+        } else {
+            stat = gi_run<2>(gi, rows, a.max_gi, iters);
+        }
+        // yaw: -(w - wmin) <= u <= wmax - w
+        const double ylo = -(e[5] - a.vmin[2]), yhi = a.vmax[2] - e[5];
+        if (ylo > yhi + a.tol * fmax(1.0, fabs(yhi))) stat = (stat == MPCCBF_STATUS_OPTIMAL) ? MPCCBF_STATUS_INFEASIBLE : stat;
+        const double uy = fmin(fmax(__ldg(du + 2), ylo), yhi);
+        const bool ok = stat == MPCCBF_STATUS_OPTIMAL;
+        a.u[g * 3 + 0] = ok ? gi.v[0] : 0.0;
+        a.u[g * 3 + 1] = ok ? gi.v[1] : 0.0;
+        a.u[g * 3 + 2] = ok ? uy : 0.0;
+        if (a.status) a.status[g] = stat;
+    }
+}
+
 __global__ void __launch_bounds__(128) cbf_filter_kernel(const FilterArgs a) {
     extern __shared__ __align__(16) double fsm[];
     const unsigned full = 0xffffffffu;
@@ -331,86 +404,204 @@ __global__ void __launch_bounds__(128) cbf_filter_kernel(const FilterArgs a) {
         }
 
         // ---- per agent: rows and the 3-variable QP --------------------------------------------------
-        if (lane < N) {
-            const int self = lane;
-            const size_t g = static_cast<size_t>(s) * N + self;
-            const double* e = st + self * 6;
-            // connectivity HOCBF row (closed form; eigenvector held constant, no range gating)
-            double gx = 0.0, gy = 0.0, hxx = 0.0, hxy = 0.0, hyy = 0.0;
+        // (slack mode: the leaders of an agent's groups take N bytes of the eigenvector matrix's storage, free by now)
+        if (lane < N) filter_agent(a, st, fv, lam2, R2, sigma, s, lane, reinterpret_cast<unsigned char*>(Vm) + lane * 32);
+        __syncwarp();
+    }
+}
+
+
+// ---- swarms of 33 .. 256 agents: one CTA of 256 threads per scenario ----------------------------------------------------
+// The Laplacian and the (transposed) eigenvector matrix no longer fit in shared memory (2 x 8 N^2 bytes): they live in a
+// per-CTA global workspace, which stays in L2. The eigen-solve is the same Jacobi iteration in its PARALLEL ordering: a
+// sweep is N - 1 rounds of N / 2 rotations on disjoint index pairs (round-robin tournament), each round = the angles from
+// the 2 x 2 blocks, then J' L and J' V' as row operations (coalesced) and L J as a column operation. Same convergence test.
+constexpr int kWideT = 256;
+
+// sum over the CTA of two values per thread; every thread returns the totals
+__device__ __forceinline__ void wide_sum2(double& x, double& y, double* red) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        x += __shfl_xor_sync(0xffffffffu, x, o);
+        y += __shfl_xor_sync(0xffffffffu, y, o);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) {
+        red[2 * w] = x;
+        red[2 * w + 1] = y;
+    }
+    __syncthreads();
+    x = 0.0;
+    y = 0.0;
+    for (int i = 0; i < kWideT / 32; ++i) {
+        x += red[2 * i];
+        y += red[2 * i + 1];
+    }
+}
+// arg-min over the CTA (ties: smaller index); every thread returns the winner
+__device__ __forceinline__ void wide_argmin(double& v, int& idx, double* red) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, v, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (ov < v || (ov == v && oi < idx)) { v = ov; idx = oi; }
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) {
+        red[2 * w] = v;
+        red[2 * w + 1] = static_cast<double>(idx);
+    }
+    __syncthreads();
+    v = red[0];
+    idx = static_cast<int>(red[1]);
+    for (int i = 1; i < kWideT / 32; ++i) {
+        const double ov = red[2 * i];
+        const int oi = static_cast<int>(red[2 * i + 1]);
+        if (ov < v || (ov == v && oi < idx)) { v = ov; idx = oi; }
+    }
+}
+
+__global__ void __launch_bounds__(kWideT) cbf_filter_wide_kernel(const FilterArgs a, double* ws_mats, unsigned char* ws_lead) {
+    extern __shared__ __align__(16) double wsm[];
+    const int N = a.N, t = threadIdx.x;
+    const int Ne = (N + 1) & ~1, half = Ne / 2;
+    double* st = wsm;            // [N][6]
+    double* fv = st + N * 6;     // [N]
+    double* rc = fv + N;         // [half] cosines of the round
+    double* rs = rc + half;      // [half] sines
+    double* red = rs + half;     // reductions
+    int* rp = reinterpret_cast<int*>(red + 2 * (kWideT / 32));  // [half] pair (p, q) of the round, p < 0: no rotation
+    int* rq = rp + half;
+    double* Lm = ws_mats + static_cast<size_t>(blockIdx.x) * 2 * N * N;
+    double* Vt = Lm + static_cast<size_t>(N) * N;   // V transposed: row i = eigenvector of the i-th diagonal entry
+    unsigned char* lead = ws_lead ? ws_lead + static_cast<size_t>(blockIdx.x) * N * N : nullptr;
+    const double R2 = a.dmax * a.dmax, sigma = R2 * R2 / log(2.0);
+
+    for (int s = blockIdx.x; s < a.S; s += gridDim.x) {
+        __syncthreads();
+        const double* src = a.states + static_cast<size_t>(s) * N * 6;
+        for (int i = t; i < N * 6; i += kWideT) st[i] = __ldg(src + i);
+        __syncthreads();
+        for (int r = t; r < N; r += kWideT) {   // Laplacian row r, V = I
+            double deg = 0.0;
             for (int j = 0; j < N; ++j) {
-                if (j == self) continue;
-                const double dx = e[0] - st[j * 6], dy = e[1] - st[j * 6 + 1];
-                const double diff = R2 - (dx * dx + dy * dy);
-                const double E = exp(diff * diff / sigma);
-                const double dvj = fv[self] - fv[j], wj = dvj * dvj;
-                const double c = -4.0 * E * diff / sigma;
-                const double cp2 = 2.0 * (4.0 * E / sigma * (2.0 * diff * diff / sigma + 1.0));
-                gx = fma(c * wj, dx, gx);
-                gy = fma(c * wj, dy, gy);
-                hxx += wj * (c + cp2 * dx * dx);
-                hxy += wj * (cp2 * dx * dy);
-                hyy += wj * (c + cp2 * dy * dy);
-            }
-            const double vx = e[3], vy = e[4];
-            const double lfh = gx * vx + gy * vy;
-            const double lf2h = vx * (hxx * vx + hxy * vy) + vy * (hxy * vx + hyy * vy);
-            const double bconn = lf2h + a.gamma * lfh + a.gamma * (lfh + a.gamma * (lam2 - 0.1));
-            if (a.conn_rows) {
-                double* r = a.conn_rows + g * 4;
-                r[0] = gx; r[1] = gy; r[2] = 0.0; r[3] = bconn;
-            }
-            if (a.u && a.desired_u) {
-                const double* du = a.desired_u + g * 3;
-                FilterRows rows;
-                rows.st = st; rows.N = N; rows.self = self;
-                rows.dmin2 = a.dmin2; rows.gamma = a.gamma; rows.tol = a.tol;
-                rows.vlo[0] = -(e[3] - a.vmin[0]); rows.vhi[0] = a.vmax[0] - e[3];
-                rows.vlo[1] = -(e[4] - a.vmin[1]); rows.vhi[1] = a.vmax[1] - e[4];
-                rows.use_conn = lam2 > 0.1;
-                rows.gx = gx; rows.gy = gy; rows.bconn = bconn;
-                GIState<2> gi;
-                const double v0[2] = {__ldg(du), __ldg(du + 1)};
-                gi_init<2>(gi, v0);
-                int iters = 0;
-                int stat;
-                if (a.slack) {
-                    // leaders of this agent's groups: N bytes in the eigenvector matrix's storage (free after fv was taken)
-                    FilterRowsSoft soft;
-                    soft.r = rows;
-                    soft.lead = reinterpret_cast<unsigned char*>(Vm) + self * 32;
-                    soft.slack_cost = a.slack_cost;
-                    soft.slack_decay = a.slack_decay;
-                    for (int gq = 0; gq < N; ++gq) soft.lead[gq] = 0;
-                    GISoft<2> gs;
-                    gs.grp[0] = gs.grp[1] = -1;
-                    gs.cap[0] = gs.cap[1] = HUGE_VAL;
-                    stat = gi_run<2, true, FilterRowsSoft>(gi, gs, soft, a.max_gi, iters, gi_vmax2<2>(v0));
-                } else {
-                    stat = gi_run<2>(gi, rows, a.max_gi, iters);
+                double w = 0.0;
+                if (j != r) {
+                    const double dx = st[r * 6] - st[j * 6], dy = st[r * 6 + 1] - st[j * 6 + 1];
+                    const double d2 = dx * dx + dy * dy;
+                    if (d2 <= R2) w = exp((R2 - d2) * (R2 - d2) / sigma) - 1.0;
                 }
-                // yaw: -(w - wmin) <= u <= wmax - w
-                const double ylo = -(e[5] - a.vmin[2]), yhi = a.vmax[2] - e[5];
-                if (ylo > yhi + a.tol * fmax(1.0, fabs(yhi))) stat = (stat == MPCCBF_STATUS_OPTIMAL) ? MPCCBF_STATUS_INFEASIBLE : stat;
-                const double uy = fmin(fmax(__ldg(du + 2), ylo), yhi);
-                const bool ok = stat == MPCCBF_STATUS_OPTIMAL;
-                a.u[g * 3 + 0] = ok ? gi.v[0] : 0.0;
-                a.u[g * 3 + 1] = ok ? gi.v[1] : 0.0;
-                a.u[g * 3 + 2] = ok ? uy : 0.0;
-                if (a.status) a.status[g] = stat;
+                Lm[static_cast<size_t>(r) * N + j] = -w;
+                Vt[static_cast<size_t>(r) * N + j] = (j == r) ? 1.0 : 0.0;
+                deg += w;
+            }
+            Lm[static_cast<size_t>(r) * N + r] = deg;
+        }
+        __syncthreads();
+        for (int sweep = 0; sweep < 60; ++sweep) {
+            double off = 0.0, dg = 0.0;
+            for (int r = t; r < N; r += kWideT)
+                for (int j = 0; j < N; ++j) {
+                    const double x = Lm[static_cast<size_t>(r) * N + j];
+                    if (j == r) dg = fma(x, x, dg); else off = fma(x, x, off);
+                }
+            wide_sum2(off, dg, red);
+            if (!(off > 4.930380657631324e-32 * dg)) break;  // eps^2, CTA-uniform
+            for (int round = 0; round < Ne - 1; ++round) {
+                if (t < half) {   // pair t of this round (circle method), its rotation from the 2 x 2 block
+                    int p0, q0;
+                    if (t == 0) { p0 = Ne - 1; q0 = round; }
+                    else { p0 = (round + t) % (Ne - 1); q0 = (round - t + Ne - 1) % (Ne - 1); }
+                    int p = min(p0, q0), q = max(p0, q0);
+                    double c = 1.0, sn = 0.0;
+                    if (q >= N) {
+                        p = -1;   // the bye of an odd N
+                    } else {
+                        const double apq = Lm[static_cast<size_t>(p) * N + q];
+                        if (apq == 0.0) {
+                            p = -1;
+                        } else {
+                            const double app = Lm[static_cast<size_t>(p) * N + p], aqq = Lm[static_cast<size_t>(q) * N + q];
+                            const double theta = (aqq - app) / (2.0 * apq);
+                            const double tt = copysign(1.0, theta) / (fabs(theta) + sqrt(fma(theta, theta, 1.0)));
+                            c = rsqrt(fma(tt, tt, 1.0));
+                            sn = tt * c;
+                        }
+                    }
+                    rc[t] = c; rs[t] = sn; rp[t] = p; rq[t] = q;
+                }
+                __syncthreads();
+                for (int e = t; e < half * N; e += kWideT) {   // rows: L <- J' L, V' <- J' V'
+                    const int i = e / N, k = e - i * N;
+                    const int p = rp[i];
+                    if (p < 0) continue;
+                    const int q = rq[i];
+                    const double c = rc[i], sn = rs[i];
+                    const size_t ip = static_cast<size_t>(p) * N + k, iq = static_cast<size_t>(q) * N + k;
+                    const double lp = Lm[ip], lq = Lm[iq];
+                    Lm[ip] = c * lp - sn * lq;
+                    Lm[iq] = sn * lp + c * lq;
+                    const double vp = Vt[ip], vq = Vt[iq];
+                    Vt[ip] = c * vp - sn * vq;
+                    Vt[iq] = sn * vp + c * vq;
+                }
+                __syncthreads();
+                for (int e = t; e < half * N; e += kWideT) {   // columns: L <- L J
+                    const int k = e / half, i = e - k * half;
+                    const int p = rp[i];
+                    if (p < 0) continue;
+                    const int q = rq[i];
+                    const double c = rc[i], sn = rs[i];
+                    const size_t ip = static_cast<size_t>(k) * N + p, iq = static_cast<size_t>(k) * N + q;
+                    const double lp = Lm[ip], lq = Lm[iq];
+                    Lm[ip] = c * lp - sn * lq;
+                    Lm[iq] = sn * lp + c * lq;
+                }
+                __syncthreads();
+                if (t < half && rp[t] >= 0) {   // the annihilated entries are exactly zero
+                    Lm[static_cast<size_t>(rp[t]) * N + rq[t]] = 0.0;
+                    Lm[static_cast<size_t>(rq[t]) * N + rp[t]] = 0.0;
+                }
+                __syncthreads();
             }
         }
-        __syncwarp();
+        // ---- second smallest eigenvalue and its (normalised) eigenvector --------------------------------------------
+        const double dv = (t < N) ? Lm[static_cast<size_t>(t) * N + t] : HUGE_VAL;
+        double m1 = dv;
+        int i1 = t;
+        wide_argmin(m1, i1, red);
+        double m2 = (t == i1) ? HUGE_VAL : dv;
+        int i2 = t;
+        wide_argmin(m2, i2, red);
+        const double lam2 = m2;
+        double x = (t < N) ? Vt[static_cast<size_t>(i2) * N + t] : 0.0, nn = x * x, unused = 0.0;
+        wide_sum2(nn, unused, red);
+        if (t < N) fv[t] = x * rsqrt(nn);
+        __syncthreads();
+        if (t == 0 && a.lambda2) a.lambda2[s] = lam2;
+        if (a.fiedler && t < N) a.fiedler[static_cast<size_t>(s) * N + t] = fv[t];
+        if (!a.conn_rows && !a.u) continue;
+        if (t < N) filter_agent(a, st, fv, lam2, R2, sigma, s, t, lead ? lead + static_cast<size_t>(t) * N : nullptr);
     }
 }
 
 }  // namespace
 
-// Returns a cudaError_t; cudaErrorInvalidValue when N > 32 (one lane per agent).
+// Returns a cudaError_t; cudaErrorInvalidValue when N > 256. Swarms of more than 32 agents need `wide_ws`: at least
+// cbf_filter_wide_ws_bytes(cfg, blocks) bytes for `blocks` resident CTAs (the grid is min(S, blocks)).
+size_t cbf_filter_wide_ws_bytes(const mpccbf_config& cfg, int blocks) {
+    const size_t N = cfg.num_agents;
+    return static_cast<size_t>(blocks) * (2 * N * N * sizeof(double) + N * N);
+}
+
 int launch_cbf_filter(const mpccbf_config& cfg, int S, const double* states, const double* desired_u, double* u,
-                      int32_t* status, double* lambda2, double* conn_rows, int sm_count, cudaStream_t stream, double* fiedler) {
+                      int32_t* status, double* lambda2, double* conn_rows, int sm_count, cudaStream_t stream, double* fiedler,
+                      void* wide_ws, int wide_blocks) {
     if (S <= 0) return cudaSuccess;
     const int N = cfg.num_agents;
-    if (N > 32 || N < 1) return cudaErrorInvalidValue;
+    if (N > 256 || N < 1) return cudaErrorInvalidValue;
     FilterArgs a;
     a.states = states; a.desired_u = desired_u; a.u = u; a.status = status; a.lambda2 = lambda2; a.conn_rows = conn_rows; a.fiedler = fiedler;
     a.S = S; a.N = N; a.NP = N | 1;
@@ -422,6 +613,16 @@ int launch_cbf_filter(const mpccbf_config& cfg, int S, const double* states, con
     a.slack = cfg.slack_mode ? 1 : 0;
     a.slack_cost = cfg.slack_cost;
     a.slack_decay = cfg.slack_decay;
+    if (N > 32) {
+        if (!wide_ws || wide_blocks < 1) return cudaErrorInvalidValue;
+        const int half = ((N + 1) & ~1) / 2;
+        const size_t smem = sizeof(double) * (N * 6 + N + 2 * half + 2 * (kWideT / 32)) + sizeof(int) * 2 * half;
+        double* mats = static_cast<double*>(wide_ws);
+        unsigned char* lead = reinterpret_cast<unsigned char*>(mats + static_cast<size_t>(wide_blocks) * 2 * N * N);
+        const int grid = S < wide_blocks ? S : wide_blocks;
+        cbf_filter_wide_kernel<<<grid, kWideT, smem, stream>>>(a, mats, lead);
+        return cudaGetLastError();
+    }
     const int threads = 128;
     const size_t per_warp = sizeof(double) * (N * 6 + 2 * N * a.NP + N);
     const size_t smem = per_warp * (threads / 32);

@@ -62,7 +62,8 @@ int launch_rollout(const double* states, const double* ctrl, const int32_t* n_cu
                    int B, const RolloutConst& rc, cudaStream_t stream);
 int launch_cbf_filter(const mpccbf_config& cfg, int S, const double* states, const double* desired_u, double* u,
                       int32_t* status, double* lambda2, double* conn_rows, int sm_count, cudaStream_t stream,
-                      double* fiedler = nullptr);
+                      double* fiedler = nullptr, void* wide_ws = nullptr, int wide_blocks = 0);
+size_t cbf_filter_wide_ws_bytes(const mpccbf_config& cfg, int blocks);  // workspace of the 33..256-agent kernel
 // Episode driver (episode.cu): one control step's worth of curve following + metric update.
 struct EpisodeArgs {
     double* states;            // [S][N][6] in: state the step was solved at; out: state after h

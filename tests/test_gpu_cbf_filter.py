@@ -58,7 +58,8 @@ def test_connectivity_rows_goldens_and_oracle(M, O):
         h.close()
 
 
-@pytest.mark.parametrize("N,S,spread", [(2, 64, 1.0), (4, 128, 1.2), (8, 128, 1.8), (16, 256, 2.5), (32, 16, 3.5)])
+@pytest.mark.parametrize("N,S,spread", [(2, 64, 1.0), (4, 128, 1.2), (8, 128, 1.8), (16, 256, 2.5), (32, 16, 3.5),
+                                        (33, 6, 3.5), (48, 4, 4.5), (65, 4, 5.0)])   # > 32: one CTA per scenario (oracle: seconds)
 def test_filter_parity(M, O, N, S, spread):
     vlim = [1.0, 1.0, 1.0]
     cfg = M.default_config(num_agents=N, d_min=0.5, d_max=3.0, max_scenarios=S, v_min=[-v for v in vlim], v_max=vlim)
@@ -76,7 +77,7 @@ def test_filter_parity(M, O, N, S, spread):
     assert clear.mean() > 0.9
     assert np.array_equal(got["status"][clear], ref["status"][clear])
     ok = (ref["status"] == 0) & clear[:, None]
-    assert ok.mean() > 0.3
+    assert ok.mean() > (0.3 if N <= 32 else 0.05)   # large random swarms: most agents' QPs are infeasible (statuses compared above)
     assert np.abs(got["u"] - ref["u"])[ok].max() < 1e-5        # north_star tolerance on controls
     assert np.abs(got["u"] - ref["u"])[ok].max() < 1e-7        # what the kernel actually achieves
     assert np.all(got["u"][~(got["status"] == 0)] == 0.0)
@@ -85,16 +86,16 @@ def test_filter_parity(M, O, N, S, spread):
 
 
 def test_filter_unsupported_and_errors(M):
-    cfg = M.default_config(num_agents=33, d_min=0.5, d_max=3.0, max_scenarios=1)
+    cfg = M.default_config(num_agents=257, d_min=0.5, d_max=3.0, max_scenarios=1)
     h = M.Handle(cfg)
     with pytest.raises(M.MpcCbfError) as e:
-        h.cbf_filter_batch_host(np.zeros((1, 33, 6)), np.zeros((1, 33, 3)))
+        h.cbf_filter_batch_host(np.zeros((1, 257, 6)), np.zeros((1, 257, 3)))
     assert e.value.code == M.ERR_UNSUPPORTED
     h.close()
 
 
 @pytest.mark.parametrize("N,S,spread,cost,decay", [(2, 64, 0.8, 1000.0, 0.2), (4, 128, 1.0, 1000.0, 0.2), (8, 128, 1.6, 1000.0, 0.2),
-                                                    (8, 128, 1.2, 10.0, 0.7), (16, 128, 2.2, 10.0, 0.8)])
+                                                    (8, 128, 1.2, 10.0, 0.7), (16, 128, 2.2, 10.0, 0.8), (34, 1, 3.0, 10.0, 0.9)])
 def test_filter_slack_mode_parity(M, O, N, S, spread, cost, decay):
     # ConnectivityControl.cpp:30-45: slack s_i on safety row i and CLF row i (shared), the last slack on the connectivity
     # row, linear cost slack_cost * slack_decay^i; velocity rows stay hard. Tight swarms: without slack many QPs are
@@ -102,7 +103,7 @@ def test_filter_slack_mode_parity(M, O, N, S, spread, cost, decay):
     vlim = [1.0, 1.0, 1.0]
     kw = dict(num_agents=N, d_min=0.5, d_max=3.0, v_min=[-v for v in vlim], v_max=vlim)
     st, du = random_swarms(S, N, 11 * N + 1, spread)
-    if N > 2:
+    if N > 2 and S > 1:
         st[1, 1, :2] = st[1, 0, :2] + [0.3, 0.0]   # inside d_min
     st[0, 0, 3] = 1.4                               # outside the velocity box (hard rows): still solvable by braking
     h0 = M.Handle(M.default_config(max_scenarios=S, **kw))
@@ -119,5 +120,5 @@ def test_filter_slack_mode_parity(M, O, N, S, spread, cost, decay):
     err = np.abs(got["u"] - ref["u"])[ok].max()
     assert err < 1e-5, err
     # slack did something: QPs that are infeasible with hard rows are solved, and solved ones can differ
-    assert ((hard["status"] != 0) & (got["status"] == 0)).any() or N == 2
+    assert ((hard["status"] != 0) & (got["status"] == 0)).any() or N == 2 or S == 1
     print(f"filter slack N={N}: max |u - oracle| {err:.2e}, hard infeasible {np.mean(hard['status'] != 0):.2f} -> slack infeasible {np.mean(got['status'] != 0):.3f}")
