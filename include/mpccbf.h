@@ -101,7 +101,7 @@ typedef struct mpccbf_config {
                                * the MPC-lifted connectivity HOCBF row at every CBF horizon step,
                                * else one distance-CLF row per neighbour and step
                                * (ConnectivityMPCCBFQPOperations.cpp:45-86,111-173). Needs
-                               * num_agents <= 32 and slack_mode = 0                        */
+                               * num_agents <= 256 and slack_mode = 0                       */
 } mpccbf_config;
 
 typedef struct mpccbf_handle mpccbf_handle;

@@ -404,6 +404,20 @@ int resolve_lanes(const mpccbf_handle* h, int64_t num_qp, bool force_auto = fals
     return lanes;
 }
 
+// Workspace of the CBF-only filter for swarms of more than 32 agents: Laplacian + eigenvector matrix (and slack-mode leaders)
+// of every resident CTA, 2 CTAs per SM, allocated on the first call that needs it.
+int ensure_filter_ws(mpccbf_handle* h) {
+    if (h->cfg.num_agents <= 32 || h->w_filter) return MPCCBF_OK;
+    const int blocks = std::max(1, std::min(h->cfg.max_scenarios, 2 * h->sm_count));
+    if (cudaMalloc(&h->w_filter, cbf_filter_wide_ws_bytes(h->cfg, blocks)) != cudaSuccess) {
+        h->w_filter = nullptr;
+        set_error("CBF-only filter: cudaMalloc of the eigen-solve workspace failed");
+        return MPCCBF_ERR_ALLOC;
+    }
+    h->w_filter_blocks = blocks;
+    return MPCCBF_OK;
+}
+
 int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_count, const double* states,
              const double* targets, int ref_mode, double* ctrl, double* ctrl_all, double* v_out, int32_t* status,
              int32_t* n_curves, double* objective, int32_t* iters, cudaStream_t stream) {
@@ -437,8 +451,11 @@ int run_step(mpccbf_handle* h, int32_t S, int32_t agent_begin, int32_t agent_cou
         h->qps += static_cast<int64_t>(a.num_qp) * h->cfg.impc_iter;
         return MPCCBF_OK;
     }
-    if (h->cfg.conn_mode) {  // one warp per scenario: Laplacian, Jacobi eigen-solve, second smallest eigenpair
-        CUDA_TRY(launch_cbf_filter(h->cfg, S, states, nullptr, nullptr, nullptr, h->w_lam2, nullptr, h->sm_count, stream, h->w_fied));
+    if (h->cfg.conn_mode) {  // Laplacian, Jacobi eigen-solve, second smallest eigenpair of every scenario (cbf_filter.cu)
+        const int wrc = ensure_filter_ws(h);
+        if (wrc != MPCCBF_OK) return wrc;
+        CUDA_TRY(launch_cbf_filter(h->cfg, S, states, nullptr, nullptr, nullptr, h->w_lam2, nullptr, h->sm_count, stream, h->w_fied,
+                                   h->w_filter, h->w_filter_blocks));
         a.lambda2 = h->w_lam2;
         a.fiedler = h->w_fied;
         h->launches += 1;
@@ -461,20 +478,6 @@ __global__ void dfma_peak_kernel(double* out, int iters, double a, double b) {
     }
     const double s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
     if (s == 123.456) out[0] = s;  // keeps the chain alive without a store in practice
-}
-
-// Workspace of the CBF-only filter for swarms of more than 32 agents: Laplacian + eigenvector matrix (and slack-mode leaders)
-// of every resident CTA, 2 CTAs per SM, allocated on the first call that needs it.
-int ensure_filter_ws(mpccbf_handle* h) {
-    if (h->cfg.num_agents <= 32 || h->w_filter) return MPCCBF_OK;
-    const int blocks = std::max(1, std::min(h->cfg.max_scenarios, 2 * h->sm_count));
-    if (cudaMalloc(&h->w_filter, cbf_filter_wide_ws_bytes(h->cfg, blocks)) != cudaSuccess) {
-        h->w_filter = nullptr;
-        set_error("CBF-only filter: cudaMalloc of the eigen-solve workspace failed");
-        return MPCCBF_ERR_ALLOC;
-    }
-    h->w_filter_blocks = blocks;
-    return MPCCBF_OK;
 }
 
 }  // namespace
@@ -557,10 +560,10 @@ int mpccbf_create(const mpccbf_config* cfg, mpccbf_handle** out) {
         mpccbf_destroy(h);
         return MPCCBF_ERR_UNSUPPORTED;
     }
-    if (h->cfg.conn_mode && (h->cfg.slack_mode || h->cfg.num_agents > 32 || h->solver != MPCCBF_SOLVER_REDUCED || !h->dev.poly)) {
+    if (h->cfg.conn_mode && (h->cfg.slack_mode || h->cfg.num_agents > 256 || h->solver != MPCCBF_SOLVER_REDUCED || !h->dev.poly)) {
         set_error("conn_mode needs slack_mode = 0 (the reference indexes the slack of the connectivity row by self_idx, out of "
-                  "range for the last robot: ConnectivityMPCCBFQPGenerator.cpp:56-58), num_agents <= 32 (one lane per agent in "
-                  "the eigen-solve) and a configuration the thread-per-agent kernel serves");
+                  "range for the last robot: ConnectivityMPCCBFQPGenerator.cpp:56-58), num_agents <= 256 (the eigen-solve's "
+                  "limit) and a configuration the thread-per-agent kernel serves");
         mpccbf_destroy(h);
         return MPCCBF_ERR_UNSUPPORTED;
     }

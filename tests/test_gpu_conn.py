@@ -11,7 +11,8 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("N,S,seed,spread,dmax", [(8, 64, 3, 1.6, 3.0), (16, 64, 5, 1.5, 2.5), (32, 8, 6, 1.4, 2.5),
-                                                   (2, 64, 4, 2.5, 1.5), (4, 64, 7, 2.45, 1.9)])
+                                                   (2, 64, 4, 2.5, 1.5), (4, 64, 7, 2.45, 1.9),
+                                                   (40, 2, 8, 1.5, 2.5)])   # > 32 agents: eigen-solve with a CTA per scenario
 def test_conn_mode_step_matches_oracle(M, O, N, S, seed, spread, dmax):
     base = dict(k_hor=20, num_pieces=4, d_min=0.8, d_max=dmax, num_agents=N, conn_mode=1)
     cfg, oc = M.default_config(max_scenarios=S, **base), O.base_config(**base)
@@ -48,6 +49,6 @@ def test_conn_mode_closed_loop_and_limits(M, O):
                     st[s, a, :3] = O.eval_curve(oc, got["ctrl_pts"][s, a], cfg.h, 0)
                     st[s, a, 3:] = O.eval_curve(oc, got["ctrl_pts"][s, a], cfg.h, 1)
     h.close()
-    for bad in (dict(slack_mode=1), dict(num_agents=40)):
+    for bad in (dict(slack_mode=1), dict(num_agents=257)):
         with pytest.raises(M.MpcCbfError):
             M.Handle(M.default_config(max_scenarios=1, **dict(base, **bad)))
